@@ -1,0 +1,370 @@
+#!/usr/bin/env python
+"""Gradient-sync + update benchmark (BASELINE.json metric: grad-sync+update steps/s).
+
+One *step* = every parameter array of the model pushed from every GPU, reduced, updated once, and
+the new weights present in every GPU's copy — the loop of the reference's own benchmark
+tools/bandwidth/measure.py:112-121 (push all, pull all, wait), with the optimizer on the store.
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--workload resnet50] [--impl reference]
+
+Prints ONE JSON line (rank 0).  `value` times the step with gradients already resident in HBM;
+`e2e` times the same step through the kvstore plugin call with HOST buffers (pinned host gradients
+copied in, updated weights copied back, both inside the timed region).  `--impl reference` times
+the reference's own CPU path (CommCPU reduce + CPU optimizer functors from oracle/_ref, or the
+bit-identical C restatement when that is absent) on the host cores.
+"""
+import argparse
+import json
+import os
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+import numpy as np  # noqa: E402
+
+WORKLOADS = {
+    # name: (shape list, dtype, optimizer, bytes/elem of the fused update, description)
+    "mlp": ("mlp", "f32", "sgd", 20, "C1 Gluon MLP 784-512-512-10 gradient set: pushpull + multi_sgd_mom_update"),
+    "resnet50": ("resnet50", "f32", "sgd", 20,
+                 "C2 ResNet-50 v1 gradient set (161 fp32 arrays, 25,557,032 params): pushpull + multi_sgd_mom_update"),
+    "bert_base_sgd": ("bert_base", "f16", "sgd", 20,
+                      "C3 BERT-base fp16 grads + fp32 masters (199 arrays, 109,482,240 params): multi_mp_sgd_mom_update"),
+    "bert_base_adam": ("bert_base", "f16", "adam", 28,
+                       "C3 BERT-base fp16 grads + fp32 masters (199 arrays, 109,482,240 params): fused mp adam_update"),
+    "bert_large": ("bert_large", "f32", "lamb", 28,
+                   "C4 BERT-large (391 fp32 arrays, 335,141,888 params): multi_lamb_update + global-norm clip"),
+}
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=300)
+    ap.add_argument("--warmup", type=int, default=10)
+    ap.add_argument("--workload", default="resnet50", choices=sorted(WORKLOADS))
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--e2e-steps", type=int, default=20)
+    ap.add_argument("--cpu-steps", type=int, default=0, help="0 = pick a count that takes ~10-20 s")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    return ap.parse_args()
+
+
+def peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        with open(p) as f:
+            d = json.load(f)
+        return float(d["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
+
+
+def opt_kwargs(kind, mp):
+    if kind == "sgd":
+        return dict(learning_rate=0.1, momentum=0.9, wd=1e-4, rescale_grad=1.0 / 256, multi_precision=mp)
+    if kind == "adam":
+        return dict(learning_rate=1e-4, beta1=0.9, beta2=0.999, epsilon=1e-8, wd=0.01,
+                    rescale_grad=1.0 / 256, multi_precision=mp)
+    return dict(learning_rate=1e-3, beta1=0.9, beta2=0.999, epsilon=1e-6, wd=0.01, bias_correction=True,
+                rescale_grad=1.0 / 256, multi_precision=mp)
+
+
+# ------------------------------------------------------------------------------------------------
+# CPU arm: the reference's CommCPU reduce + CPU optimizer functors on the host cores
+# ------------------------------------------------------------------------------------------------
+def cpu_run(args, ncopies, steps, warmup, budget_s=None):
+    from mxnet_maintenance_b200 import shapes
+    from oracle.oracle import Oracle, have_ref, adam_lr
+    shp_name, dt, kind, _, _ = WORKLOADS[args.workload]
+    shp = shapes.CONFIGS[shp_name]()
+    backend = "ref" if have_ref() else "port"
+    cores = os.cpu_count() or 1
+    o = Oracle(backend, nthread=cores)
+    rng = np.random.default_rng(1234)
+    wdt = np.float16 if dt == "f16" else np.float32
+    w = [rng.uniform(-1, 1, s).astype(np.float32).astype(wdt).reshape(-1) for s in shp]
+    g = [[(rng.uniform(-1, 1, s) * 1e-2).astype(np.float32).astype(wdt).reshape(-1) for s in shp]
+         for _ in range(ncopies)]
+    n = len(shp)
+    mp = dt == "f16"
+    w32 = [x.astype(np.float32) for x in w] if mp else None
+    s0 = [np.zeros(x.size, np.float32) for x in w]
+    s1 = [np.zeros(x.size, np.float32) for x in w]
+    kw = opt_kwargs(kind, mp)
+    merged = [np.empty_like(x) for x in w]
+
+    def step(t):
+        # CommCPU::Reduce copies src[0] into the merge buffer, then ReduceSumCPU (comm.h:121-207)
+        for k in range(n):
+            np.copyto(merged[k], g[0][k])
+            if ncopies > 1:
+                o.reduce_sum([merged[k]] + [g[c][k] for c in range(1, ncopies)], nthread=min(4, cores))
+        if kind == "sgd":
+            o.multi_sgd(w, merged, s0, w32, [kw["learning_rate"]] * n, [kw["wd"]] * n, kw["momentum"],
+                        kw["rescale_grad"], -1.0)
+        elif kind == "adam":
+            lr = adam_lr(kw["learning_rate"], kw["beta1"], kw["beta2"], t)
+            for k in range(n):   # Adam has no aggregated path in the reference (aggregate_num = 0)
+                if mp:
+                    o.mp_adam(w[k], merged[k], w32[k], s0[k], s1[k], lr, kw["wd"], beta1=kw["beta1"],
+                              beta2=kw["beta2"], eps=kw["epsilon"], rescale=kw["rescale_grad"])
+                else:
+                    o.adam(w[k], merged[k], s0[k], s1[k], lr, kw["wd"], kw["beta1"], kw["beta2"],
+                           kw["epsilon"], kw["rescale_grad"])
+        else:
+            if backend == "port":
+                o.clip_global_norm(merged, 1.0)
+            else:
+                Oracle("port", nthread=cores).clip_global_norm(merged, 1.0)
+            o.multi_lamb(w, merged, s0, s1, w32, [kw["learning_rate"]] * n, [kw["wd"]] * n, [t] * n,
+                         kw["beta1"], kw["beta2"], kw["epsilon"], kw["rescale_grad"])
+        # CommCPU::Broadcast: copy the stored value to every device copy (comm.h:209-224)
+        for c in range(ncopies):
+            for k in range(n):
+                np.copyto(g[c][k], w[k])
+
+    for t in range(1, warmup + 1):
+        step(t)
+    t0 = time.perf_counter()
+    done = 0
+    for t in range(warmup + 1, warmup + steps + 1):
+        step(t)
+        done += 1
+        if budget_s is not None and time.perf_counter() - t0 > budget_s and done >= 3:
+            break
+    dt_s = time.perf_counter() - t0
+    return done / dt_s, done, cores, ("reference" if backend == "ref" else "port")
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    shp_name, dt, kind, bpe, desc = WORKLOADS[args.workload]
+    steps = args.steps if args.steps <= 50 else 50
+    sps, done, cores, kind_s = cpu_run(args, max(args.gpus, 1), steps, min(args.warmup, 3), budget_s=120)
+    line = {
+        "impl": "reference", "metric": "grad-sync+update steps/s", "value": sps, "unit": "steps/s",
+        "n_gpus": args.gpus, "steps": done, "warmup": min(args.warmup, 3), "ms_per_step": 1e3 / sps,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": dt,
+        "data": "synthetic",
+        "config": {"workload": desc, "device_copies": max(args.gpus, 1), "optimizer": kind,
+                   "where": "host cores: CommCPU reduce + CPU optimizer functors + broadcast memcpy, "
+                            "gradients already in host memory"},
+        "cpu_baseline": {"value": sps, "unit": "steps/s", "cores": cores, "kind": kind_s,
+                         "sample": "%d full steps of the same workload" % done},
+        "e2e": {"value": sps, "unit": "steps/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+# ------------------------------------------------------------------------------------------------
+# clocks sampler (NVML): SM clock + throttle reasons DURING the timed region
+# ------------------------------------------------------------------------------------------------
+class Clocks:
+    def __init__(self, index):
+        self.samples, self.reasons, self.stop = [], set(), False
+        self.max_mhz = None
+        self.active = False
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.max_mhz = pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM)
+            self.th = threading.Thread(target=self._loop, daemon=True)
+            self.th.start()
+        except Exception as e:  # pragma: no cover
+            self.nv = None
+            self.err = str(e)
+
+    def _loop(self):
+        nv = self.nv
+        names = {
+            getattr(nv, "nvmlClocksEventReasonHwSlowdown", 0x8): "hw_slowdown",
+            getattr(nv, "nvmlClocksEventReasonHwThermalSlowdown", 0x40): "hw_thermal_slowdown",
+            getattr(nv, "nvmlClocksEventReasonSwThermalSlowdown", 0x20): "sw_thermal_slowdown",
+            getattr(nv, "nvmlClocksEventReasonSwPowerCap", 0x4): "sw_power_cap",
+        }
+        while not self.stop:
+            if self.active:
+                try:
+                    self.samples.append(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM))
+                    try:
+                        r = nv.nvmlDeviceGetCurrentClocksEventReasons(self.h)
+                    except Exception:
+                        r = nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
+                    for bit, name in names.items():
+                        if r & bit:
+                            self.reasons.add(name)
+                except Exception:
+                    pass
+            time.sleep(0.002)
+
+    def result(self):
+        self.stop = True
+        if self.nv is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "error": getattr(self, "err", "")}
+        s = sorted(self.samples)
+        return {"sm_mhz": (s[len(s) // 2] if s else None), "sm_max_mhz": self.max_mhz,
+                "reasons": sorted(self.reasons), "samples": len(s)}
+
+
+# ------------------------------------------------------------------------------------------------
+def run_b200(args):
+    import torch
+    import torch.distributed as dist
+    import mxnet_maintenance_b200 as mb
+    from mxnet_maintenance_b200 import shapes
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    assert world == max(args.gpus, 1), "launch with torchrun --nproc-per-node %d" % args.gpus
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+
+    shp_name, dt, kind, bpe, desc = WORKLOADS[args.workload]
+    shp = shapes.CONFIGS[shp_name]()
+    nelem = sum(shapes.numel(s) for s in shp)
+    mp = dt == "f16"
+    tdt = torch.float16 if mp else torch.float32
+    esz = 2 if mp else 4
+    gen = torch.Generator(device=dev)
+    gen.manual_seed(1234 + rank)
+    wgen = torch.Generator(device=dev)
+    wgen.manual_seed(99)
+    weights = [(torch.rand(s, device=dev, generator=wgen) * 2 - 1).to(tdt) for s in shp]
+    grads = [((torch.rand(s, device=dev, generator=gen) * 2 - 1) * 1e-2).to(tdt) for s in shp]
+    keys = list(range(len(shp)))
+
+    kv = mb.create("b200")
+    O = getattr(mb.optimizer, {"sgd": "SGD", "adam": "Adam", "lamb": "LAMB"}[kind])
+    kv.set_optimizer(O(**opt_kwargs(kind, mp)))
+    if kind == "lamb":
+        kv.clip_global_norm = 1.0
+    outs = [[w] for w in weights]
+    kv.broadcast(keys, weights, outs)
+    kv.wait()
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    clocks = Clocks(local) if rank == 0 else None
+
+    # ---- value: gradients resident in HBM -------------------------------------------------------
+    for _ in range(max(args.warmup, 3)):
+        kv.pushpull(keys, grads, out=outs)
+    barrier()
+    l0 = kv.launch_count()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    if clocks:
+        clocks.active = True
+    e0.record()
+    for _ in range(args.steps):
+        kv.pushpull(keys, grads, out=outs)
+    e1.record()
+    barrier()
+    ms = e0.elapsed_time(e1)
+    launches = kv.launch_count() - l0
+    if world > 1:
+        t = torch.tensor([ms], device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = float(t.item())
+    ms_step = ms / args.steps
+    sps = 1e3 / ms_step
+
+    # ---- e2e: host gradients in, host weights out, through the plugin call ------------------------
+    h_g = [torch.empty(g.shape, dtype=tdt).pin_memory().copy_(g) for g in grads]
+    h_w = [torch.empty(w.shape, dtype=tdt).pin_memory() for w in weights]
+    def e2e_step():
+        for d, h in zip(grads, h_g):
+            d.copy_(h, non_blocking=True)
+        kv.pushpull(keys, grads, out=outs)
+        for h, d in zip(h_w, weights):
+            h.copy_(d, non_blocking=True)
+    for _ in range(3):
+        e2e_step()
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(args.e2e_steps):
+        e2e_step()
+    barrier()
+    e2e_s = time.perf_counter() - t0
+    if world > 1:
+        t = torch.tensor([e2e_s], device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        e2e_s = float(t.item())
+    if clocks:
+        clocks.active = False
+    e2e_sps = args.e2e_steps / e2e_s
+
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+
+    # ---- roofline --------------------------------------------------------------------------------
+    peak, peak_src = peaks()
+    if world == 1:
+        alg = float(bpe) * nelem
+        ach = alg / (ms_step * 1e-3) / 1e9
+        roof = {"bound": "hbm", "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
+                "traffic": None, "kernel": "mta_kernel (fused multi-tensor %s update)" % kind,
+                "algorithmic_bytes_per_launch": alg, "bytes_per_element": bpe,
+                "launches_per_step": launches / args.steps,
+                "peak_source": peak_src,
+                "note": "achieved uses the whole step time (table upload + kernel[s]) from CUDA events"}
+    else:
+        # un-overlapped lower bound of SURVEY.md §8(d): RS + AG over NVLink + sharded update in HBM
+        sbytes = float(nelem) * esz
+        t_coll = 2.0 * sbytes * (world - 1) / world / 900e9
+        t_upd = float(bpe) * nelem / world / (peak * 1e9)
+        bound_s = t_coll + t_upd
+        bus = 2.0 * sbytes * (world - 1) / world / (ms_step * 1e-3) / 1e9
+        roof = {"bound": "nvlink", "achieved": bus, "peak": 900.0, "unit": "GB/s", "frac": bus / 900.0,
+                "traffic": None, "kernel": "ncclReduceScatter + sharded update + ncclAllGather",
+                "step_lower_bound_ms": bound_s * 1e3, "step_frac_of_lower_bound": bound_s * 1e3 / ms_step,
+                "note": "achieved = NCCL bus-bandwidth convention 2*S*(N-1)/N / step time, peak = nominal "
+                        "NVLink 5 900 GB/s per direction"}
+
+    line = {
+        "metric": "grad-sync+update steps/s", "value": sps, "unit": "steps/s", "n_gpus": world,
+        "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": ms_step,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": dt, "data": "synthetic",
+        "config": {"workload": desc, "optimizer": kind, "update_on_kvstore": True,
+                   "l2": "working set %.0f MB per step exceeds the 126 MB L2; no flush needed"
+                         % ((esz * 2 + (16 if kind != "sgd" else 8) + (4 if mp else 0)) * nelem / 1e6),
+                   "parallelism": "dp%d reduce-scatter / sharded update / all-gather" % world if world > 1
+                                  else "single GPU, fused update in place"},
+        "roofline": roof,
+        "e2e": {"value": e2e_sps, "unit": "steps/s", "h2d_bytes_per_step": nelem * esz,
+                "d2h_bytes_per_step": nelem * esz, "steps": args.e2e_steps,
+                "what": "pinned host gradients -> device, kvstore.pushpull, updated weights -> pinned host"},
+        "gpu_launches": launches,
+        "clocks": clocks.result() if clocks else None,
+    }
+    if not args.no_cpu_baseline and world == 1:
+        cpu_steps = args.cpu_steps or 200
+        cs, done, cores, kind_s = cpu_run(args, 1, cpu_steps, 2, budget_s=15)
+        line["cpu_baseline"] = {"value": cs, "unit": "steps/s", "cores": cores, "kind": kind_s,
+                                "sample": "%d full steps of the same workload on the host cores, gradients "
+                                          "already in host memory" % done}
+    print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    a = parse()
+    if a.impl == "reference":
+        run_reference(a)
+    else:
+        run_b200(a)

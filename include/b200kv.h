@@ -1,0 +1,209 @@
+/*
+ * b200kv — C ABI of the B200-native gradient-sync + update library (libb200kv.so).
+ *
+ * Drop-in boundary for MXNet 1.x's kvstore hot path.  Every entry point returns 0 on success and
+ * -1 on failure with a thread-local message retrievable through b200kv_last_error(), the same
+ * convention as the reference C API (include/mxnet/c_api_error.h:36-55, MXGetLastError in
+ * src/c_api/c_api_error.cc:195-206).  C++ exceptions never cross this boundary.
+ *
+ * Tensors are handed over zero-copy as DLPack `DLManagedTensor*` (the struct MXNDArrayToDLPack
+ * produces, include/mxnet/c_api.h:994-1038; 3rdparty/dlpack/include/dlpack/dlpack.h).  They are
+ * BORROWED for the duration of the call: the library never calls `deleter` and never frees caller
+ * memory.  Tensors must be compact row-major CUDA tensors on the store's device.
+ *
+ * One store drives ONE GPU; several processes (one per GPU) form a communicator
+ * (b200kv_comm_unique_id / b200kv_comm_init).  Within a process a key may be pushed as several
+ * device-local copies (the reference's "one value per device" lists); they are summed in the
+ * reference's CommCPU order before the cross-GPU reduction.
+ *
+ * All work is enqueued on the stream given to b200kv_set_stream (default: the legacy default
+ * stream, which orders with MXNet's blocking streams); b200kv_wait blocks until it has drained.
+ */
+#ifndef B200KV_H_
+#define B200KV_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* ---- DLPack (binary-identical to dlpack.h v0.2 .. v0.8 unversioned DLManagedTensor) ---------- */
+#ifndef DLPACK_DLPACK_H_
+#ifndef DLPACK_VERSION
+typedef enum { kDLCPU = 1, kDLCUDA = 2, kDLCUDAHost = 3 } DLDeviceType;
+typedef struct { int32_t device_type; int32_t device_id; } DLDevice;
+typedef enum { kDLInt = 0U, kDLUInt = 1U, kDLFloat = 2U } DLDataTypeCode;
+typedef struct { uint8_t code; uint8_t bits; uint16_t lanes; } DLDataType;
+typedef struct {
+  void* data;
+  DLDevice device;
+  int32_t ndim;
+  DLDataType dtype;
+  int64_t* shape;
+  int64_t* strides;
+  uint64_t byte_offset;
+} DLTensor;
+typedef struct DLManagedTensor {
+  DLTensor dl_tensor;
+  void* manager_ctx;
+  void (*deleter)(struct DLManagedTensor* self);
+} DLManagedTensor;
+#endif
+#endif
+
+typedef void* b200kv_handle;
+
+/* MXGetLastError (src/c_api/c_api_error.cc:195-206) */
+const char* b200kv_last_error(void);
+/* library version: major*10000 + minor*100 + patch */
+int b200kv_version(int* out);
+
+/* ============================ store: replaces MXKVStore* ======================================
+ * Reference block: include/mxnet/c_api.h:2720-3140, impl src/c_api/c_api.cc:2534-2975,
+ * semantics src/kvstore/kvstore_local.h:226-343. */
+
+/* MXKVStoreCreate (c_api.h:2727) + KVStore::Create (src/kvstore/kvstore.cc:41-82).
+ * device_id: CUDA ordinal this store drives.  rank/world_size: position among the cooperating
+ * processes (MXKVStoreGetRank / MXKVStoreGetGroupSize). */
+int b200kv_create(int device_id, int rank, int world_size, b200kv_handle* out);
+/* MXKVStoreFree (c_api.h:2741) */
+int b200kv_free(b200kv_handle h);
+/* stream all subsequent work is enqueued on (a cudaStream_t passed as an integer/pointer) */
+int b200kv_set_stream(b200kv_handle h, void* cuda_stream);
+/* block the caller until everything enqueued by this store has completed
+ * (the role of NDArray::WaitToRead on the results in the reference) */
+int b200kv_wait(b200kv_handle h);
+
+/* KVStoreNCCL::InitNCCL (src/kvstore/kvstore_nccl.h:475-493).  Rank 0 obtains a 128-byte id,
+ * the host side ships it to the other processes, every rank then calls b200kv_comm_init. */
+int b200kv_comm_unique_id(char out_id[128]);
+int b200kv_comm_init(b200kv_handle h, const char id[128]);
+
+/* KVStoreLocal::LookupKeys (kvstore_local.h:449-457): string keys -> int keys.  create != 0
+ * registers unknown names (init); otherwise an unknown name is an error. Mixing int and string
+ * keys in one store is an error (kvstore_local.h:322-325). */
+int b200kv_lookup_keys(b200kv_handle h, int num, const char* const* str_keys, int create,
+                       int* out_keys);
+
+/* MXKVStoreInit (c_api.h:2752): copies each value into the store; duplicate key -> error
+ * (kvstore_local.h:229-232).  With several processes the value of rank 0 is broadcast. */
+int b200kv_init(b200kv_handle h, int num, const int* keys, DLManagedTensor* const* vals);
+/* MXKVStorePush (c_api.h:2790): entries with equal keys are device copies of one key
+ * (GroupKVPairs, kvstore_local.h:417-447).  Reduce, then run the optimizer on the stored value,
+ * or assign the merged value when none is set (kvstore_local.h:239-276). */
+int b200kv_push(b200kv_handle h, int num, const int* keys, DLManagedTensor* const* vals,
+                int priority);
+/* MXKVStorePullWithSparse (c_api.h:2830): copy the stored value into every out
+ * (kvstore_local.h:278-292). */
+int b200kv_pull(b200kv_handle h, int num, const int* keys, DLManagedTensor* const* outs,
+                int priority);
+/* MXKVStorePushPull (c_api.h:2920): push then pull, fused into one pass
+ * (kvstore_local.h:336-343). */
+int b200kv_pushpull(b200kv_handle h, int vnum, const int* vkeys, DLManagedTensor* const* vals,
+                    int onum, const int* okeys, DLManagedTensor* const* outs, int priority);
+/* MXKVStoreBroadcast (c_api.h:2880): init + pull (kvstore_local.h:327-334). */
+int b200kv_broadcast(b200kv_handle h, int vnum, const int* vkeys, DLManagedTensor* const* vals,
+                     int onum, const int* okeys, DLManagedTensor* const* outs, int priority);
+
+/* ---- optimizer on the store: replaces MXKVStoreSetUpdaterEx + the Python updater callback ----
+ * (c_api.h:2985-3020; kvstore_local.h:259-267; python/mxnet/optimizer/optimizer.py:2070-2127).
+ * The host side keeps the Optimizer's scheduler / multiplier logic and ships resolved scalars,
+ * exactly the attributes that reach multi_sgd_mom_update / adam_update / multi_lamb_update. */
+enum { B200KV_OPT_NONE = 0, B200KV_OPT_SGD = 1, B200KV_OPT_ADAM = 2, B200KV_OPT_LAMB = 3 };
+typedef struct {
+  int32_t kind;             /* B200KV_OPT_* */
+  int32_t multi_precision;  /* fp16 weights keep an fp32 master copy (optimizer.py:252-304,583-600) */
+  int32_t bias_correction;  /* LAMB (multi_lamb-inl.h:51-105) */
+  float momentum;           /* SGD; 0 = no momentum state */
+  float beta1, beta2, epsilon;
+  float rescale_grad, clip_gradient;   /* clip_gradient < 0: off */
+  float lower_bound, upper_bound;      /* LAMB; < 0: off */
+  float clip_global_norm;              /* gluon.utils.clip_global_norm max_norm applied to the
+                                          merged gradients of one push; < 0: off */
+} b200kv_optimizer;
+int b200kv_set_optimizer(b200kv_handle h, const b200kv_optimizer* opt);
+/* per-key scalars for the next update: learning rate (for Adam already bias-corrected, as
+ * optimizer.py:1616-1619 does), weight decay, update count t (LAMB bias correction). */
+int b200kv_set_hyper(b200kv_handle h, int num, const int* keys, const float* lrs, const float* wds,
+                     const int* steps);
+/* after a push with clip_global_norm >= 0: the total gradient norm of that push (blocks) */
+int b200kv_last_global_norm(b200kv_handle h, float* out);
+
+/* optimizer-state access for Trainer.save_states/load_states (python/mxnet/kvstore/kvstore.py:641-690,
+ * optimizer.py:2142-2160).  which: 0 = momentum/mean, 1 = var, 2 = fp32 master weight.
+ * get: copies the key's state into `out` (fp32, same element count); *present = 0 if that state
+ * does not exist yet.  Collective when world_size > 1 (state is sharded across ranks). */
+int b200kv_get_state(b200kv_handle h, int key, int which, DLManagedTensor* out, int* present);
+int b200kv_set_state(b200kv_handle h, int key, int which, DLManagedTensor* in);
+
+/* ---- row-sparse keys ---------------------------------------------------------------------------
+ * MXKVStoreInit with a row_sparse NDArray: `dense_value` is the [num_rows, row_len] table. */
+int b200kv_init_rsp(b200kv_handle h, int key, DLManagedTensor* dense_value);
+/* Push of `ncopies` row-sparse gradients (indices int64 sorted unique [nnr_k], values
+ * [nnr_k, row_len]; a copy with nnr 0 is skipped like an uninitialised NDArray):
+ * CommDevice::ReduceRowSparse / ElementwiseSumRsp (src/kvstore/comm.h:478-501,
+ * src/ndarray/ndarray_function.cc:59-176) then the lazy row update (sgd_mom_update / adam_update
+ * FComputeEx, optimizer_op-inl.h:747-802,1342-1409) or assignment of the merged rows. */
+int b200kv_push_rsp(b200kv_handle h, int key, int ncopies, DLManagedTensor* const* indices,
+                    DLManagedTensor* const* values, int priority);
+/* the merged gradient of the last b200kv_push_rsp on this key: row count, then a copy-out
+ * (indices int64 [nnr], values [nnr,row_len]) for callers that need it */
+int b200kv_rsp_merged_size(b200kv_handle h, int key, int64_t* nnr);
+int b200kv_rsp_merged_copy(b200kv_handle h, int key, DLManagedTensor* out_indices,
+                           DLManagedTensor* out_values);
+/* MXKVStorePullRowSparse (c_api.h:2960; kvstore_local.h:294-314,468-512; kvstore_utils.cu:44-110;
+ * sparse_retain-inl.h:262-323): row_ids may be any shape / int or float dtype, unsorted, with
+ * duplicates.  out_indices (int64) and out_values must hold at least numel(row_ids) rows;
+ * *out_nnr receives the number of unique ids; rows absent from the store come back as zeros. */
+int b200kv_row_sparse_pull(b200kv_handle h, int key, DLManagedTensor* row_ids,
+                           DLManagedTensor* out_indices, DLManagedTensor* out_values,
+                           int64_t* out_nnr, int priority);
+
+/* MXKVStoreGetType / GetRank / GetGroupSize / Barrier (c_api.h:3040-3100) */
+int b200kv_get_type(b200kv_handle h, const char** out);
+int b200kv_get_rank(b200kv_handle h, int* out);
+int b200kv_get_group_size(b200kv_handle h, int* out);
+int b200kv_barrier(b200kv_handle h);
+/* number of kernels this store has launched so far (bench.py's gpu_launches) */
+int b200kv_launch_count(b200kv_handle h, int64_t* out);
+
+/* ============================ operators: replace the NNVM optimizer ops =======================
+ * Direct, store-less forms of the fused multi-tensor ops a local Updater calls when
+ * update_on_kvstore=False (python/mxnet/optimizer/optimizer.py:602-669,1316-1361).  Arrays are raw
+ * device pointers; every pointer array has `num` entries; all updates are in place.
+ * dtype: 0 = float32 everywhere; 2 = float16 weights/grads with float32 states and `weights32`
+ * master copies (the multi_mp_* variants).  stream: cudaStream_t. */
+
+/* multi_sgd_update / multi_sgd_mom_update / multi_mp_sgd_update / multi_mp_sgd_mom_update
+ * (src/operator/optimizer_op-inl.h:207-380; registration optimizer_op.cc:322-506).
+ * moms == NULL selects the momentum-free forms. */
+int b200kv_multi_sgd_update(int num, int dtype, void* const* weights, const void* const* grads,
+                            float* const* moms, float* const* weights32, const int64_t* sizes,
+                            const float* lrs, const float* wds, float momentum, float rescale_grad,
+                            float clip_gradient, void* stream);
+/* adam_update over a tensor list (optimizer_op-inl.h:1252-1340); dtype 2 is the fused form of
+ * the multi-precision wrapper (optimizer.py:298-304). */
+int b200kv_multi_adam_update(int num, int dtype, void* const* weights, const void* const* grads,
+                             float* const* means, float* const* vars, float* const* weights32,
+                             const int64_t* sizes, const float* lrs, const float* wds, float beta1,
+                             float beta2, float epsilon, float rescale_grad, float clip_gradient,
+                             void* stream);
+/* _multi_lamb_update / _multi_mp_lamb_update (src/operator/contrib/multi_lamb-inl.h:51-340,
+ * multi_lamb.cc:33-251, multi_lamb.cu:35-258); no 45-tensor limit. */
+int b200kv_multi_lamb_update(int num, int dtype, void* const* weights, const void* const* grads,
+                             float* const* means, float* const* vars, float* const* weights32,
+                             const int64_t* sizes, const float* lrs, const float* wds,
+                             const int* step_counts, float beta1, float beta2, float epsilon,
+                             float rescale_grad, float clip_gradient, float lower_bound,
+                             float upper_bound, int bias_correction, void* stream);
+/* multi_sum_sq (src/operator/contrib/multi_sum_sq-inl.h:88-103, .cu:84-205): out[i] = sum(x_i^2),
+ * fp32, deterministic (no atomics).  `out` is a device pointer to `num` floats. */
+int b200kv_multi_sum_sq(int num, int dtype, const void* const* arrays, const int64_t* sizes,
+                        float* out, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200KV_H_ */

@@ -1,0 +1,405 @@
+// extern "C" boundary: every entry point returns 0 / -1 and records the failure text for
+// b200kv_last_error(), like MXNet's API_BEGIN/API_END (include/mxnet/c_api_error.h:36-55).
+#include <cmath>
+#include <cstring>
+#include <mutex>
+
+#include "nccl_dl.h"
+#include "store.h"
+
+namespace b200kv {
+const char* get_last_error();
+}
+
+using namespace b200kv;
+
+#define API_BEGIN() try {
+#define API_END()                                   \
+  }                                                 \
+  catch (const std::exception& e) {                 \
+    b200kv::set_last_error(e.what());               \
+    return -1;                                      \
+  }                                                 \
+  catch (...) {                                     \
+    b200kv::set_last_error("unknown C++ exception");\
+    return -1;                                      \
+  }                                                 \
+  return 0;
+
+static Store* S(b200kv_handle h) {
+  KV_CHECK(h != nullptr, "null store handle");
+  return static_cast<Store*>(h);
+}
+
+extern "C" {
+
+const char* b200kv_last_error(void) { return b200kv::get_last_error(); }
+
+int b200kv_version(int* out) {
+  API_BEGIN();
+  *out = 100;  // 0.1.0
+  API_END();
+}
+
+int b200kv_create(int device_id, int rank, int world_size, b200kv_handle* out) {
+  API_BEGIN();
+  *out = new Store(device_id, rank, world_size);
+  API_END();
+}
+
+int b200kv_free(b200kv_handle h) {
+  API_BEGIN();
+  delete S(h);
+  API_END();
+}
+
+int b200kv_set_stream(b200kv_handle h, void* cuda_stream) {
+  API_BEGIN();
+  S(h)->set_stream(static_cast<cudaStream_t>(cuda_stream));
+  API_END();
+}
+
+int b200kv_wait(b200kv_handle h) {
+  API_BEGIN();
+  S(h)->wait();
+  API_END();
+}
+
+int b200kv_comm_unique_id(char out_id[128]) {
+  API_BEGIN();
+  ncclUniqueId id;
+  NCCL_OK(NcclApi::get().GetUniqueId(&id));
+  std::memcpy(out_id, &id, 128);
+  API_END();
+}
+
+int b200kv_comm_init(b200kv_handle h, const char id[128]) {
+  API_BEGIN();
+  S(h)->comm_init(id);
+  API_END();
+}
+
+int b200kv_lookup_keys(b200kv_handle h, int num, const char* const* str_keys, int create,
+                       int* out_keys) {
+  API_BEGIN();
+  S(h)->lookup_keys(num, str_keys, create != 0, out_keys);
+  API_END();
+}
+
+int b200kv_init(b200kv_handle h, int num, const int* keys, DLManagedTensor* const* vals) {
+  API_BEGIN();
+  S(h)->init(num, keys, vals);
+  API_END();
+}
+
+int b200kv_push(b200kv_handle h, int num, const int* keys, DLManagedTensor* const* vals, int) {
+  API_BEGIN();
+  S(h)->dense(Store::kPush, num, keys, vals, 0, nullptr, nullptr);
+  API_END();
+}
+
+int b200kv_pull(b200kv_handle h, int num, const int* keys, DLManagedTensor* const* outs, int) {
+  API_BEGIN();
+  S(h)->dense(Store::kPull, 0, nullptr, nullptr, num, keys, outs);
+  API_END();
+}
+
+int b200kv_pushpull(b200kv_handle h, int vnum, const int* vkeys, DLManagedTensor* const* vals,
+                    int onum, const int* okeys, DLManagedTensor* const* outs, int) {
+  API_BEGIN();
+  S(h)->dense(Store::kPushPull, vnum, vkeys, vals, onum, okeys, outs);
+  API_END();
+}
+
+int b200kv_broadcast(b200kv_handle h, int vnum, const int* vkeys, DLManagedTensor* const* vals,
+                     int onum, const int* okeys, DLManagedTensor* const* outs, int) {
+  API_BEGIN();
+  // BroadcastImpl = InitImpl; PullImpl (kvstore_local.h:327-334)
+  S(h)->init(vnum, vkeys, vals);
+  S(h)->dense(Store::kPull, 0, nullptr, nullptr, onum, okeys, outs);
+  API_END();
+}
+
+int b200kv_set_optimizer(b200kv_handle h, const b200kv_optimizer* opt) {
+  API_BEGIN();
+  KV_CHECK(opt != nullptr, "null optimizer description");
+  S(h)->set_optimizer(*opt);
+  API_END();
+}
+
+int b200kv_set_hyper(b200kv_handle h, int num, const int* keys, const float* lrs, const float* wds,
+                     const int* steps) {
+  API_BEGIN();
+  S(h)->set_hyper(num, keys, lrs, wds, steps);
+  API_END();
+}
+
+int b200kv_last_global_norm(b200kv_handle h, float* out) {
+  API_BEGIN();
+  *out = S(h)->last_global_norm();
+  API_END();
+}
+
+int b200kv_get_state(b200kv_handle h, int key, int which, DLManagedTensor* out, int* present) {
+  API_BEGIN();
+  S(h)->get_state(key, which, out, present);
+  API_END();
+}
+
+int b200kv_set_state(b200kv_handle h, int key, int which, DLManagedTensor* in) {
+  API_BEGIN();
+  S(h)->set_state(key, which, in);
+  API_END();
+}
+
+int b200kv_init_rsp(b200kv_handle h, int key, DLManagedTensor* dense_value) {
+  API_BEGIN();
+  S(h)->init_rsp(key, dense_value);
+  API_END();
+}
+
+int b200kv_push_rsp(b200kv_handle h, int key, int ncopies, DLManagedTensor* const* indices,
+                    DLManagedTensor* const* values, int) {
+  API_BEGIN();
+  S(h)->push_rsp(key, ncopies, indices, values);
+  API_END();
+}
+
+int b200kv_rsp_merged_size(b200kv_handle h, int key, int64_t* nnr) {
+  API_BEGIN();
+  *nnr = S(h)->rsp_merged_size(key);
+  API_END();
+}
+
+int b200kv_rsp_merged_copy(b200kv_handle h, int key, DLManagedTensor* out_indices,
+                           DLManagedTensor* out_values) {
+  API_BEGIN();
+  S(h)->rsp_merged_copy(key, out_indices, out_values);
+  API_END();
+}
+
+int b200kv_row_sparse_pull(b200kv_handle h, int key, DLManagedTensor* row_ids,
+                           DLManagedTensor* out_indices, DLManagedTensor* out_values,
+                           int64_t* out_nnr, int) {
+  API_BEGIN();
+  *out_nnr = S(h)->row_sparse_pull(key, row_ids, out_indices, out_values);
+  API_END();
+}
+
+int b200kv_get_type(b200kv_handle h, const char** out) {
+  API_BEGIN();
+  *out = S(h)->type();
+  API_END();
+}
+
+int b200kv_get_rank(b200kv_handle h, int* out) {
+  API_BEGIN();
+  *out = S(h)->rank();
+  API_END();
+}
+
+int b200kv_get_group_size(b200kv_handle h, int* out) {
+  API_BEGIN();
+  *out = S(h)->world();
+  API_END();
+}
+
+int b200kv_barrier(b200kv_handle h) {
+  API_BEGIN();
+  S(h)->barrier();
+  API_END();
+}
+
+int b200kv_launch_count(b200kv_handle h, int64_t* out) {
+  API_BEGIN();
+  *out = S(h)->launches();
+  API_END();
+}
+
+}  // extern "C"
+
+// =================================================================================================
+// Operator entry points: the fused multi-tensor ops on caller-owned arrays (no store).
+// =================================================================================================
+namespace {
+
+// Per-device workspace for the operator calls: the tensor table ring, a cached chunk plan (rebuilt
+// only when the size list changes) and the small reduction scratch.
+struct OpWorkspace {
+  TableRing ring;
+  ChunkPlan plan;
+  std::vector<int64_t> sizes;
+  DevBuf partials, sums;
+  std::mutex mu;
+};
+
+OpWorkspace& workspace(int device) {
+  static std::mutex mu;
+  static OpWorkspace* ws[64] = {nullptr};
+  std::lock_guard<std::mutex> lk(mu);
+  KV_CHECK(device >= 0 && device < 64, "device ordinal out of range");
+  if (!ws[device]) ws[device] = new OpWorkspace();
+  return *ws[device];
+}
+
+int current_device() {
+  int d = 0;
+  CUDA_OK(cudaGetDevice(&d));
+  return d;
+}
+
+void prepare_plan(OpWorkspace& w, int num, const int64_t* sizes) {
+  std::vector<int64_t> sz(sizes, sizes + num);
+  if (sz != w.sizes || w.plan.nt != num) {
+    std::vector<int64_t> b(num, 0);
+    w.plan.build(b, sz);
+    w.sizes = sz;
+    w.partials.reserve(sizeof(float) * 2 * static_cast<size_t>(std::max(w.plan.nchunks, 1)));
+    w.sums.reserve(sizeof(float) * (3 * static_cast<size_t>(num) + 4));
+  }
+}
+
+struct Table {
+  uint64_t* p;
+  int nt, ng, no;
+  void G(int k, int t, const void* x) { p[static_cast<size_t>(k) * nt + t] = reinterpret_cast<uint64_t>(x); }
+  void Sx(int sec, int t, const void* x) { p[static_cast<size_t>(ng + no + sec) * nt + t] = reinterpret_cast<uint64_t>(x); }
+  void F2(int sec, int t, float a, float b) {
+    float v[2] = {a, b};
+    std::memcpy(&p[static_cast<size_t>(ng + no + sec) * nt + t], v, 8);
+  }
+};
+
+// Fills the table for an in-place update of caller arrays.  For dtype fp16 (multi-precision) the
+// W section is the fp32 master and the fp16 weight is the single out copy.
+MtaCall make_call(OpWorkspace& w, int num, int dtype, void* const* weights, const void* const* grads,
+                  float* const* s0, float* const* s1, float* const* w32, const float* lrs,
+                  const float* wds, const float* aux0, const float* aux1, cudaStream_t stream,
+                  int device) {
+  KV_CHECK(dtype == kF32 || dtype == kF16, "dtype must be 0 (float32) or 2 (float16 + fp32 master)");
+  const bool mp = dtype == kF16;
+  KV_CHECK(!mp || w32 != nullptr, "float16 weights need weights32 master copies");
+  const int ng = grads ? 1 : 0, no = mp ? 1 : 0;
+  const int ngl = ng ? ng : 1;   // the table always carries one gradient section
+  Table t{w.ring.begin(mta_blob_words(num, ngl, no) * 8), num, ngl, no};
+  std::memset(t.p, 0, mta_blob_words(num, ngl, no) * 8);
+  for (int i = 0; i < num; ++i) {
+    if (grads) t.G(0, i, grads[i]);
+    if (mp) { t.G(ngl, i, weights[i]); t.Sx(kSecW, i, w32[i]); }   // out section follows the grads
+    else t.Sx(kSecW, i, weights[i]);
+    if (s0) t.Sx(kSecS0, i, s0[i]);
+    if (s1) t.Sx(kSecS1, i, s1[i]);
+    t.F2(kSecLrWd, i, lrs ? lrs[i] : 0.f, wds ? wds[i] : 0.f);
+    t.F2(kSecAux, i, aux0 ? aux0[i] : 0.f, aux1 ? aux1[i] : 0.f);
+  }
+  MtaCall c;
+  c.blob = w.ring.commit(stream);
+  c.plan = &w.plan;
+  c.nt = num; c.ngrad = ngl; c.nout = no; c.dtype = dtype; c.stream = stream; c.device = device;
+  return c;
+}
+
+}  // namespace
+
+extern "C" {
+
+int b200kv_multi_sgd_update(int num, int dtype, void* const* weights, const void* const* grads,
+                            float* const* moms, float* const* weights32, const int64_t* sizes,
+                            const float* lrs, const float* wds, float momentum, float rescale_grad,
+                            float clip_gradient, void* stream) {
+  API_BEGIN();
+  if (num <= 0) return 0;
+  const int dev = current_device();
+  OpWorkspace& w = workspace(dev);
+  std::lock_guard<std::mutex> lk(w.mu);
+  prepare_plan(w, num, sizes);
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  MtaCall c = make_call(w, num, dtype, weights, grads, moms, nullptr, weights32, lrs, wds, nullptr,
+                        nullptr, st, dev);
+  OptScalars s;
+  s.momentum = momentum; s.rescale = rescale_grad; s.clip = clip_gradient;
+  launch_sgd(c, moms != nullptr, s, nullptr);
+  w.ring.end(st);
+  API_END();
+}
+
+int b200kv_multi_adam_update(int num, int dtype, void* const* weights, const void* const* grads,
+                             float* const* means, float* const* vars, float* const* weights32,
+                             const int64_t* sizes, const float* lrs, const float* wds, float beta1,
+                             float beta2, float epsilon, float rescale_grad, float clip_gradient,
+                             void* stream) {
+  API_BEGIN();
+  if (num <= 0) return 0;
+  const int dev = current_device();
+  OpWorkspace& w = workspace(dev);
+  std::lock_guard<std::mutex> lk(w.mu);
+  prepare_plan(w, num, sizes);
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  MtaCall c = make_call(w, num, dtype, weights, grads, means, vars, weights32, lrs, wds, nullptr,
+                        nullptr, st, dev);
+  OptScalars s;
+  s.beta1 = beta1; s.beta2 = beta2; s.eps = epsilon; s.rescale = rescale_grad; s.clip = clip_gradient;
+  launch_adam(c, s, nullptr);
+  w.ring.end(st);
+  API_END();
+}
+
+int b200kv_multi_lamb_update(int num, int dtype, void* const* weights, const void* const* grads,
+                             float* const* means, float* const* vars, float* const* weights32,
+                             const int64_t* sizes, const float* lrs, const float* wds,
+                             const int* step_counts, float beta1, float beta2, float epsilon,
+                             float rescale_grad, float clip_gradient, float lower_bound,
+                             float upper_bound, int bias_correction, void* stream) {
+  API_BEGIN();
+  if (num <= 0) return 0;
+  const int dev = current_device();
+  OpWorkspace& w = workspace(dev);
+  std::lock_guard<std::mutex> lk(w.mu);
+  prepare_plan(w, num, sizes);
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  std::vector<float> c1(num), c2(num);
+  for (int i = 0; i < num; ++i) {
+    const float tf = static_cast<float>(step_counts[i]);
+    c1[i] = 1.0f - powf(beta1, tf);
+    c2[i] = 1.0f - powf(beta2, tf);
+  }
+  MtaCall c = make_call(w, num, dtype, weights, grads, means, vars, weights32, lrs, wds, c1.data(),
+                        c2.data(), st, dev);
+  OptScalars s;
+  s.beta1 = beta1; s.beta2 = beta2; s.eps = epsilon; s.rescale = rescale_grad; s.clip = clip_gradient;
+  s.lower = lower_bound; s.upper = upper_bound; s.bias_correction = bias_correction;
+  float* partials = w.partials.as<float>();
+  float* sums = w.sums.as<float>();
+  float* ratio = sums + 2 * static_cast<size_t>(num);
+  launch_lamb1(c, s, nullptr, partials);
+  launch_reduce_partials(partials, w.plan, 2, sums, st);
+  launch_lamb_ratio(sums, num, lower_bound, upper_bound, ratio, st);
+  launch_lamb2(c, s, ratio);
+  w.ring.end(st);
+  API_END();
+}
+
+int b200kv_multi_sum_sq(int num, int dtype, const void* const* arrays, const int64_t* sizes,
+                        float* out, void* stream) {
+  API_BEGIN();
+  if (num <= 0) return 0;
+  const int dev = current_device();
+  OpWorkspace& w = workspace(dev);
+  std::lock_guard<std::mutex> lk(w.mu);
+  prepare_plan(w, num, sizes);
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  KV_CHECK(dtype == kF32 || dtype == kF16, "dtype must be 0 (float32) or 2 (float16)");
+  Table t{w.ring.begin(mta_blob_words(num, 1, 0) * 8), num, 1, 0};
+  std::memset(t.p, 0, mta_blob_words(num, 1, 0) * 8);
+  for (int i = 0; i < num; ++i) t.G(0, i, arrays[i]);
+  MtaCall c;
+  c.blob = w.ring.commit(st);
+  c.plan = &w.plan;
+  c.nt = num; c.ngrad = 1; c.nout = 0; c.dtype = dtype; c.stream = st; c.device = dev;
+  launch_sumsq(c, w.partials.as<float>());
+  launch_reduce_partials(w.partials.as<float>(), w.plan, 1, out, st);
+  w.ring.end(st);
+  API_END();
+}
+
+}  // extern "C"

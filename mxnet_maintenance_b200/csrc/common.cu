@@ -1,0 +1,126 @@
+#include "common.h"
+
+#include <cstring>
+#include <mutex>
+
+namespace b200kv {
+
+static thread_local std::string g_last_error;
+void set_last_error(const std::string& msg) { g_last_error = msg; }
+const char* get_last_error() { return g_last_error.c_str(); }
+
+TensorView view_of(const DLManagedTensor* t, int device_id, const char* what) {
+  KV_CHECK(t != nullptr, what << ": null DLManagedTensor");
+  const DLTensor& d = t->dl_tensor;
+  KV_CHECK(d.device.device_type == kDLCUDA,
+           what << ": tensor must live in CUDA device memory (DLPack device_type "
+                << d.device.device_type << ")");
+  KV_CHECK(d.device.device_id == device_id, what << ": tensor is on device " << d.device.device_id
+                                                 << " but the store drives device " << device_id);
+  KV_CHECK(d.dtype.lanes == 1, what << ": vector lanes unsupported");
+  KV_CHECK(d.ndim >= 0 && d.ndim <= 8, what << ": unsupported ndim " << d.ndim);
+  TensorView v;
+  if (d.dtype.code == kDLFloat && d.dtype.bits == 32) v.dtype = kF32;
+  else if (d.dtype.code == kDLFloat && d.dtype.bits == 16) v.dtype = kF16;
+  else if (d.dtype.code == kDLInt && d.dtype.bits == 64) v.dtype = kI64;
+  else if (d.dtype.code == kDLInt && d.dtype.bits == 32) v.dtype = kI32;
+  else KV_CHECK(false, what << ": unsupported dtype code " << int(d.dtype.code) << " bits "
+                            << int(d.dtype.bits));
+  v.ndim = d.ndim;
+  v.numel = 1;
+  for (int i = 0; i < d.ndim; ++i) {
+    v.shape[i] = d.shape[i];
+    v.numel *= d.shape[i];
+  }
+  if (d.strides != nullptr) {  // MXNet only accepts compact row-major (tensor_blob.h:116-137)
+    int64_t expect = 1;
+    for (int i = d.ndim - 1; i >= 0; --i) {
+      KV_CHECK(d.shape[i] <= 1 || d.strides[i] == expect, what << ": tensor is not compact row-major");
+      expect *= d.shape[i];
+    }
+  }
+  v.data = static_cast<char*>(d.data) + d.byte_offset;
+  return v;
+}
+
+// ---- TableRing ---------------------------------------------------------------------------------
+TableRing::~TableRing() {
+  for (auto& s : slots_) {
+    if (s.host) cudaFreeHost(s.host);
+    if (s.dev) cudaFree(s.dev);
+    if (s.done) cudaEventDestroy(s.done);
+  }
+}
+
+uint64_t* TableRing::begin(size_t bytes) {
+  cur_ = (cur_ + 1) % kSlots;
+  Slot& s = slots_[cur_];
+  if (s.busy) {  // the launches that read this slot's previous table must have finished
+    CUDA_OK(cudaEventSynchronize(s.done));
+    s.busy = false;
+  }
+  if (bytes > s.cap) {
+    if (s.host) cudaFreeHost(s.host);
+    if (s.dev) cudaFree(s.dev);
+    s.host = s.dev = nullptr;
+    const size_t cap = (bytes + 4095) & ~size_t(4095);
+    CUDA_OK(cudaMallocHost(&s.host, cap));
+    CUDA_OK(cudaMalloc(&s.dev, cap));
+    s.cap = cap;
+  }
+  if (!s.done) CUDA_OK(cudaEventCreateWithFlags(&s.done, cudaEventDisableTiming));
+  cur_bytes_ = bytes;
+  return static_cast<uint64_t*>(s.host);
+}
+
+const uint64_t* TableRing::commit(cudaStream_t stream) {
+  Slot& s = slots_[cur_];
+  CUDA_OK(cudaMemcpyAsync(s.dev, s.host, cur_bytes_, cudaMemcpyHostToDevice, stream));
+  return static_cast<const uint64_t*>(s.dev);
+}
+
+void TableRing::end(cudaStream_t stream) {
+  Slot& s = slots_[cur_];
+  CUDA_OK(cudaEventRecord(s.done, stream));
+  s.busy = true;
+}
+
+// ---- ChunkPlan ---------------------------------------------------------------------------------
+void ChunkPlan::build(const std::vector<int64_t>& begin, const std::vector<int64_t>& end) {
+  nt = static_cast<int>(begin.size());
+  std::vector<Chunk> ch;
+  std::vector<int> fst(nt + 1, 0);
+  for (int t = 0; t < nt; ++t) {
+    fst[t] = static_cast<int>(ch.size());
+    for (int64_t o = begin[t]; o < end[t]; o += kChunk) {
+      Chunk c;
+      c.tensor = t;
+      c.off = o;
+      c.len = static_cast<int32_t>(end[t] - o < kChunk ? end[t] - o : kChunk);
+      ch.push_back(c);
+    }
+  }
+  fst[nt] = static_cast<int>(ch.size());
+  nchunks = static_cast<int>(ch.size());
+  chunks.reserve(sizeof(Chunk) * (ch.empty() ? 1 : ch.size()));
+  first.reserve(sizeof(int) * fst.size());
+  if (!ch.empty())
+    CUDA_OK(cudaMemcpy(chunks.p, ch.data(), sizeof(Chunk) * ch.size(), cudaMemcpyHostToDevice));
+  CUDA_OK(cudaMemcpy(first.p, fst.data(), sizeof(int) * fst.size(), cudaMemcpyHostToDevice));
+}
+
+int sm_count(int device) {
+  static std::mutex mu;
+  static int cache[64] = {0};
+  std::lock_guard<std::mutex> lk(mu);
+  if (device < 0 || device >= 64) return 148;
+  if (cache[device] == 0) {
+    int n = 0;
+    if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, device) != cudaSuccess || n <= 0)
+      n = 148;
+    cache[device] = n;
+  }
+  return cache[device];
+}
+
+}  // namespace b200kv

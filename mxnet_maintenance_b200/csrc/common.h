@@ -1,0 +1,119 @@
+// Host-side plumbing shared by the store and the operator entry points.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include <sstream>
+#include <stdexcept>
+#include <string>
+#include <vector>
+
+#include "../../include/b200kv.h"
+#include "mta.h"
+
+namespace b200kv {
+
+struct Error : public std::runtime_error {
+  explicit Error(const std::string& m) : std::runtime_error(m) {}
+};
+
+#define KV_CHECK(cond, msg)                                                      \
+  do {                                                                           \
+    if (!(cond)) {                                                               \
+      std::ostringstream os_;                                                    \
+      os_ << msg << " [" << __FILE__ << ":" << __LINE__ << "]";                  \
+      throw ::b200kv::Error(os_.str());                                          \
+    }                                                                            \
+  } while (0)
+
+#define CUDA_OK(expr)                                                            \
+  do {                                                                           \
+    cudaError_t e_ = (expr);                                                     \
+    if (e_ != cudaSuccess) {                                                     \
+      std::ostringstream os_;                                                    \
+      os_ << "CUDA error: " << cudaGetErrorString(e_) << " in " #expr " ["       \
+          << __FILE__ << ":" << __LINE__ << "]";                                 \
+      throw ::b200kv::Error(os_.str());                                          \
+    }                                                                            \
+  } while (0)
+
+void set_last_error(const std::string& msg);
+
+// mshadow type flags (3rdparty/mshadow/mshadow/base.h): the dtype codes MXNet itself uses
+enum DType { kF32 = 0, kF16 = 2, kI32 = 4, kI64 = 6 };
+inline size_t dtype_size(int dt) { return dt == kF32 || dt == kI32 ? 4 : (dt == kF16 ? 2 : 8); }
+
+// A validated view of a borrowed DLPack tensor
+struct TensorView {
+  void* data = nullptr;
+  int64_t numel = 0;
+  int dtype = kF32;
+  int ndim = 0;
+  int64_t shape[8] = {0};
+};
+TensorView view_of(const DLManagedTensor* t, int device_id, const char* what);
+
+// grow-only device buffer
+struct DevBuf {
+  void* p = nullptr;
+  size_t bytes = 0;
+  DevBuf() = default;
+  DevBuf(const DevBuf&) = delete;
+  DevBuf& operator=(const DevBuf&) = delete;
+  ~DevBuf() { release(); }
+  void release() {
+    if (p) cudaFree(p);
+    p = nullptr;
+    bytes = 0;
+  }
+  // returns true when the buffer was (re)allocated; contents are NOT preserved
+  bool reserve(size_t n) {
+    if (n <= bytes) return false;
+    release();
+    CUDA_OK(cudaMalloc(&p, n));
+    bytes = n;
+    return true;
+  }
+  template <typename T> T* as() const { return static_cast<T*>(p); }
+};
+
+// Ring of pinned-host + device staging slots for the per-call tensor tables, so a call never
+// overwrites a table an earlier, still-running launch is reading.
+class TableRing {
+ public:
+  static constexpr int kSlots = 8;
+  TableRing() = default;
+  ~TableRing();
+  // returns a host pointer to fill (bytes) for the next slot
+  uint64_t* begin(size_t bytes);
+  // uploads the slot on `stream`; returns the device address of the table
+  const uint64_t* commit(cudaStream_t stream);
+  // call after the launches that read the committed table have been enqueued
+  void end(cudaStream_t stream);
+
+ private:
+  struct Slot {
+    void* host = nullptr;
+    void* dev = nullptr;
+    size_t cap = 0;
+    cudaEvent_t done = nullptr;
+    bool busy = false;
+  };
+  Slot slots_[kSlots];
+  int cur_ = -1;
+  size_t cur_bytes_ = 0;
+};
+
+// A chunk list + per-tensor chunk ranges resident on the device
+struct ChunkPlan {
+  DevBuf chunks;   // Chunk[nchunks]
+  DevBuf first;    // int[nt + 1]
+  int nchunks = 0;
+  int nt = 0;
+  // ranges: per tensor [begin, end) element range to cover (relative to tensor element 0)
+  void build(const std::vector<int64_t>& begin, const std::vector<int64_t>& end);
+};
+
+int sm_count(int device);
+
+}  // namespace b200kv

@@ -1,0 +1,43 @@
+// Host launchers of the multi-tensor kernels (defined in optim.cu).
+#pragma once
+#include "common.h"
+
+namespace b200kv {
+
+struct MtaCall {
+  const uint64_t* blob = nullptr;   // device table (see mta.h)
+  const ChunkPlan* plan = nullptr;
+  int nt = 0, ngrad = 1, nout = 0;
+  int dtype = kF32;                 // element type of grads / outs: kF32 | kF16
+  cudaStream_t stream = nullptr;
+  int device = 0;
+};
+
+struct OptScalars {
+  float momentum = 0.f, beta1 = 0.9f, beta2 = 0.999f, eps = 1e-8f;
+  float rescale = 1.f, clip = -1.f, lower = -1.f, upper = -1.f;
+  int bias_correction = 1;
+};
+
+// Each launcher returns the number of kernels it enqueued.
+// Update kernels: W section is the fp32 weight (dtype kF32) or the fp32 master (dtype kF16).
+int launch_sgd(const MtaCall& c, bool has_mom, const OptScalars& s, const float* gscale);
+int launch_adam(const MtaCall& c, const OptScalars& s, const float* gscale);
+// partials: [nchunks][2] floats
+int launch_lamb1(const MtaCall& c, const OptScalars& s, const float* gscale, float* partials);
+int launch_lamb2(const MtaCall& c, const OptScalars& s, const float* ratio);
+// partials: [nchunks] floats; squares of the G section (ngrad copies summed first)
+int launch_sumsq(const MtaCall& c, float* partials);
+// W section <- sum of the G copies; optionally also to the out copies.  The W section holds
+// `dtype` elements, or fp32 when w_is_f32 (fp16 value -> fp32 master).
+int launch_copy(const MtaCall& c, bool to_w, bool to_out, bool w_is_f32 = false);
+// out copies (dtype) <- W section (fp32 master)
+int launch_master_to_out(const MtaCall& c);
+
+int launch_reduce_partials(const float* partials, const ChunkPlan& plan, int nred, float* sums,
+                           cudaStream_t stream);
+int launch_lamb_ratio(const float* sums, int nt, float lower, float upper, float* ratio,
+                      cudaStream_t stream);
+int launch_global_norm(const float* sums, int nt, float max_norm, float* out2, cudaStream_t stream);
+
+}  // namespace b200kv

@@ -1,0 +1,42 @@
+// Multi-tensor-apply tables shared by host and device code.
+//
+// One kernel launch covers every parameter array of a model: the launch gets a device-resident
+// table of per-tensor base pointers / sizes / scalars and a list of fixed-size chunks; a block
+// works on one chunk at a time.  This replaces the reference's by-value MultiSGDKernelParam /
+// MultiLAMBKernelParam structs (src/operator/optimizer_op-inl.h:207-223, contrib/multi_lamb-inl.h:191-213)
+// that cap a launch at 60 / 45 tensors and make thread i touch element i of *every* tensor.
+#pragma once
+#include <stdint.h>
+
+namespace b200kv {
+
+// elements per chunk: 256 threads x 4 elements x 4 unrolled vectors
+constexpr int kChunk = 4096;
+constexpr int kThreads = 256;
+constexpr int kMaxCopies = 8;   // local gradient / output copies per key handled in one launch
+
+struct Chunk {          // 16 bytes
+  int32_t tensor;       // row of the tensor table
+  int32_t len;          // elements in this chunk (<= kChunk)
+  int64_t off;          // element offset inside the tensor
+};
+
+// The table is one blob of 8-byte words laid out as consecutive sections of `nt` words each:
+//   grad[0..ngrad) | out[0..nout) | w | s0 | s1 | size | (lr,wd) | (aux0,aux1)
+// Pointers are per-tensor element-0 addresses; a section may hold nulls when unused.
+struct MtaArgs {
+  const uint64_t* blob;
+  const Chunk* chunks;
+  int nchunks;
+  int nt;
+  int ngrad;
+  int nout;
+};
+
+inline size_t mta_blob_words(int nt, int ngrad, int nout) {
+  return static_cast<size_t>(nt) * static_cast<size_t>(ngrad + nout + 6);
+}
+
+enum Section { kSecW = 0, kSecS0 = 1, kSecS1 = 2, kSecSize = 3, kSecLrWd = 4, kSecAux = 5 };
+
+}  // namespace b200kv

@@ -1,0 +1,438 @@
+// Multi-tensor update kernels for sm_100a: one launch per optimizer step over a device-side
+// pointer/size table (mta.h), 128-bit coalesced loads/stores, chunk-per-block.
+//
+// Arithmetic is written with explicit round-to-nearest intrinsics (__fmul_rn/__fadd_rn/...) in the
+// reference functors' evaluation order, so nvcc never contracts into FMA and fp32 results are
+// bit-identical with the reference's CPU kernels:
+//   SGD   MultiSGDKernel::Map        src/operator/optimizer_op-inl.h:225-258
+//   Adam  AdamUpdateKernel::Map      src/operator/optimizer_op-inl.h:1293-1315
+//   LAMB  MultiLAMBKernelStep1/2     src/operator/contrib/multi_lamb.cc:33-118
+//   sumsq CalcSumSq                  src/operator/contrib/multi_sum_sq.cc:68-84 (values; order differs)
+//   local copy sum  CommCPU::ReduceSumCPU  src/kvstore/comm.h:357-392 (same grouping => same bits)
+#pragma once
+#include <cuda_fp16.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "mta.h"
+
+namespace b200kv {
+
+constexpr int kU = 4;  // 128-bit vectors per thread per chunk
+
+// ------------------------------------------------------------------------------------------------
+// element-type helpers
+// ------------------------------------------------------------------------------------------------
+__device__ __forceinline__ void ld4(const float* p, float (&v)[4]) {
+  const float4 x = *reinterpret_cast<const float4*>(p);
+  v[0] = x.x; v[1] = x.y; v[2] = x.z; v[3] = x.w;
+}
+__device__ __forceinline__ void ld4(const __half* p, float (&v)[4]) {
+  const uint2 raw = *reinterpret_cast<const uint2*>(p);
+  const float2 a = __half22float2(*reinterpret_cast<const __half2*>(&raw.x));
+  const float2 b = __half22float2(*reinterpret_cast<const __half2*>(&raw.y));
+  v[0] = a.x; v[1] = a.y; v[2] = b.x; v[3] = b.y;
+}
+__device__ __forceinline__ void st4(float* p, const float (&v)[4]) {
+  *reinterpret_cast<float4*>(p) = make_float4(v[0], v[1], v[2], v[3]);
+}
+__device__ __forceinline__ void st4(__half* p, const float (&v)[4]) {
+  // fp32 -> fp16 is round-to-nearest-even, like F16C _cvtss_sh(x, 0) in mshadow/half.h:340-349
+  const __half2 a = __floats2half2_rn(v[0], v[1]);
+  const __half2 b = __floats2half2_rn(v[2], v[3]);
+  uint2 raw;
+  raw.x = *reinterpret_cast<const uint32_t*>(&a);
+  raw.y = *reinterpret_cast<const uint32_t*>(&b);
+  *reinterpret_cast<uint2*>(p) = raw;
+}
+__device__ __forceinline__ float ld1(const float* p) { return *p; }
+__device__ __forceinline__ float ld1(const __half* p) { return __half2float(*p); }
+__device__ __forceinline__ void st1(float* p, float v) { *p = v; }
+__device__ __forceinline__ void st1(__half* p, float v) { *p = __float2half_rn(v); }
+
+// value of x after a round trip through the tensor's element type
+template <typename T> __device__ __forceinline__ float round_to(float x);
+template <> __device__ __forceinline__ float round_to<float>(float x) { return x; }
+template <> __device__ __forceinline__ float round_to<__half>(float x) {
+  return __half2float(__float2half_rn(x));
+}
+// DType add: fp32 add, rounded to the element type after every add (half.h:64-85)
+template <typename T> __device__ __forceinline__ float add_as(float a, float b) {
+  return round_to<T>(__fadd_rn(a, b));
+}
+
+__device__ __forceinline__ float clipf(float x, float b) {  // mshadow_op::clip, mshadow_op.h:1022-1032
+  return x > b ? b : (x < -b ? -b : x);
+}
+
+__device__ __forceinline__ const uint64_t* sec_grad(const MtaArgs& a, int k) {
+  return a.blob + static_cast<size_t>(k) * a.nt;
+}
+__device__ __forceinline__ const uint64_t* sec_out(const MtaArgs& a, int k) {
+  return a.blob + static_cast<size_t>(a.ngrad + k) * a.nt;
+}
+__device__ __forceinline__ const uint64_t* sec(const MtaArgs& a, int s) {
+  return a.blob + static_cast<size_t>(a.ngrad + a.nout + s) * a.nt;
+}
+
+// ------------------------------------------------------------------------------------------------
+// gradient fetch: NG == 1 is the hot path; NG == 0 means "a.ngrad copies, summed in CommCPU order"
+//   acc = g0;  acc += g1 (+ g2 (+ g3 (+ g4)));  acc += g5 + ...       (comm.h:362-391)
+// ------------------------------------------------------------------------------------------------
+template <typename T, int NG>
+__device__ __forceinline__ void grad4(const MtaArgs& a, int t, int64_t e, float (&g)[4]) {
+  ld4(reinterpret_cast<const T*>(sec_grad(a, 0)[t]) + e, g);
+  if (NG == 0) {
+    for (int i = 1; i < a.ngrad; i += 4) {
+      float s[4];
+      ld4(reinterpret_cast<const T*>(sec_grad(a, i)[t]) + e, s);
+      for (int k = 1; k < 4 && i + k < a.ngrad; ++k) {
+        float x[4];
+        ld4(reinterpret_cast<const T*>(sec_grad(a, i + k)[t]) + e, x);
+#pragma unroll
+        for (int j = 0; j < 4; ++j) s[j] = add_as<T>(s[j], x[j]);
+      }
+#pragma unroll
+      for (int j = 0; j < 4; ++j) g[j] = add_as<T>(g[j], s[j]);
+    }
+  }
+}
+template <typename T, int NG>
+__device__ __forceinline__ float grad1(const MtaArgs& a, int t, int64_t e) {
+  float g = ld1(reinterpret_cast<const T*>(sec_grad(a, 0)[t]) + e);
+  if (NG == 0) {
+    for (int i = 1; i < a.ngrad; i += 4) {
+      float s = ld1(reinterpret_cast<const T*>(sec_grad(a, i)[t]) + e);
+      for (int k = 1; k < 4 && i + k < a.ngrad; ++k)
+        s = add_as<T>(s, ld1(reinterpret_cast<const T*>(sec_grad(a, i + k)[t]) + e));
+      g = add_as<T>(g, s);
+    }
+  }
+  return g;
+}
+
+// ------------------------------------------------------------------------------------------------
+// element operators.  Flags tell the generic kernel which arrays to touch.
+// ------------------------------------------------------------------------------------------------
+struct OpFlags {
+  bool read_g, read_w, write_w, write_out, read_s0, write_s0, read_s1, write_s1;
+  int nred;
+};
+
+// multi_sgd_update / multi_sgd_mom_update / multi_mp_sgd(_mom)_update
+template <bool HAS_MOM>
+struct SgdOp {
+  static constexpr OpFlags F = {true, true, true, true, HAS_MOM, HAS_MOM, false, false, 0};
+  float momentum, rescale, clip;
+  struct PT { float lr, lrwd, lrrs; };
+  __device__ __forceinline__ PT prep(float lr, float wd, float, float) const {
+    return {lr, __fmul_rn(lr, wd), __fmul_rn(lr, rescale)};
+  }
+  template <typename T>
+  __device__ __forceinline__ void elem(const PT& p, float& w, float g, float& s0, float&,
+                                       float*) const {
+    float mom = HAS_MOM ? s0 : 0.0f;
+    const float a = __fmul_rn(momentum, mom);
+    const float b = __fmul_rn(p.lrwd, w);
+    const float c = clip >= 0.0f ? __fmul_rn(p.lr, clipf(__fmul_rn(rescale, g), clip))
+                                 : __fmul_rn(p.lrrs, g);
+    mom = __fsub_rn(__fsub_rn(a, b), c);
+    s0 = mom;
+    w = __fadd_rn(w, mom);
+  }
+};
+
+// adam_update (bias correction already folded into lr by the host, optimizer.py:1616-1619);
+// with fp16 weights/grads this is the fused form of Optimizer.update_multi_precision
+// (optimizer.py:298-304): cast grad -> fp32, update master, cast master -> fp16 weight.
+struct AdamOp {
+  static constexpr OpFlags F = {true, true, true, true, true, true, true, true, 0};
+  float beta1, beta2, eps, rescale, clip;
+  struct PT { float lr, wd, omb1, omb2; };
+  __device__ __forceinline__ PT prep(float lr, float wd, float, float) const {
+    return {lr, wd, __fsub_rn(1.f, beta1), __fsub_rn(1.f, beta2)};
+  }
+  template <typename T>
+  __device__ __forceinline__ void elem(const PT& p, float& w, float g, float& m, float& v,
+                                       float*) const {
+    float gr = __fadd_rn(__fmul_rn(g, rescale), __fmul_rn(w, p.wd));
+    if (clip >= 0.f) gr = clipf(gr, clip);
+    m = __fadd_rn(__fmul_rn(beta1, m), __fmul_rn(p.omb1, gr));
+    v = __fadd_rn(__fmul_rn(beta2, v), __fmul_rn(__fmul_rn(p.omb2, gr), gr));
+    w = __fsub_rn(w, __fdiv_rn(__fmul_rn(p.lr, m), __fadd_rn(__fsqrt_rn(v), eps)));
+  }
+};
+
+// LAMB update direction u = m_hat/(sqrt(v_hat)+eps) + wd*w   (multi_lamb.cc:56-72)
+// aux0 = 1 - beta1^t, aux1 = 1 - beta2^t (computed with the host's powf, as the CPU kernel does)
+__device__ __forceinline__ float lamb_dir(float m, float v, float w, float wd, float c1, float c2,
+                                          float eps, bool bias_correction) {
+  if (bias_correction) {
+    const float mh = __fdiv_rn(m, c1);
+    const float vh = __fdiv_rn(v, c2);
+    return __fadd_rn(__fdiv_rn(mh, __fadd_rn(__fsqrt_rn(vh), eps)), __fmul_rn(wd, w));
+  }
+  return __fadd_rn(__fdiv_rn(m, __fadd_rn(__fsqrt_rn(v), eps)), __fmul_rn(wd, w));
+}
+
+// pass 1: moments, and per-chunk partial sums of w^2 (in the weight dtype, multi_lamb-inl.h:286-289)
+// and u^2.  u is not stored: pass 2 recomputes it from the new m, v and the unchanged w, which
+// costs the same HBM bytes as writing and re-reading a temp_g buffer but no scratch memory.
+struct Lamb1Op {
+  static constexpr OpFlags F = {true, true, false, false, true, true, true, true, 2};
+  float beta1, beta2, eps, rescale, clip;
+  int bias_correction;
+  struct PT { float wd, c1, c2, omb1, omb2; };
+  __device__ __forceinline__ PT prep(float, float wd, float a0, float a1) const {
+    return {wd, a0, a1, __fsub_rn(1.f, beta1), __fsub_rn(1.f, beta2)};
+  }
+  template <typename T>
+  __device__ __forceinline__ void elem(const PT& p, float& w, float g, float& m, float& v,
+                                       float* red) const {
+    float sg = __fmul_rn(g, rescale);
+    if (clip >= 0.0f) sg = clipf(sg, clip);
+    m = __fadd_rn(__fmul_rn(beta1, m), __fmul_rn(p.omb1, sg));
+    v = __fadd_rn(__fmul_rn(beta2, v), __fmul_rn(__fmul_rn(p.omb2, sg), sg));
+    const float u = lamb_dir(m, v, w, p.wd, p.c1, p.c2, eps, bias_correction != 0);
+    const float wt = round_to<T>(w);
+    red[0] = __fadd_rn(red[0], round_to<T>(__fmul_rn(wt, wt)));
+    red[1] = __fadd_rn(red[1], __fmul_rn(u, u));
+  }
+};
+
+// pass 2: w -= lr * ratio * u   (multi_lamb.cc:79-118).  aux0/aux1 as in pass 1; the per-tensor
+// trust ratio is read from `ratio[t]` (device array produced by lamb_ratio_kernel).
+struct Lamb2Op {
+  static constexpr OpFlags F = {false, true, true, true, true, false, true, false, 0};
+  float eps;
+  int bias_correction;
+  const float* ratio;
+  struct PT { float wd, c1, c2, lr_adj; };
+  __device__ __forceinline__ PT prep_t(float lr, float wd, float a0, float a1, int t) const {
+    return {wd, a0, a1, __fmul_rn(lr, ratio[t])};
+  }
+  template <typename T>
+  __device__ __forceinline__ void elem(const PT& p, float& w, float, float& m, float& v,
+                                       float*) const {
+    const float u = lamb_dir(m, v, w, p.wd, p.c1, p.c2, eps, bias_correction != 0);
+    w = __fsub_rn(w, __fmul_rn(p.lr_adj, u));
+  }
+};
+
+// multi_sum_sq: per-chunk partial sums of g^2 (product rounded to the element type first, as
+// half_t * half_t does on the CPU path)
+struct SumSqOp {
+  static constexpr OpFlags F = {true, false, false, false, false, false, false, false, 1};
+  struct PT {};
+  __device__ __forceinline__ PT prep(float, float, float, float) const { return {}; }
+  template <typename T>
+  __device__ __forceinline__ void elem(const PT&, float&, float g, float&, float&,
+                                       float* red) const {
+    red[0] = __fadd_rn(red[0], round_to<T>(__fmul_rn(g, g)));
+  }
+};
+
+// copy (pack into a flat bucket / assign merged value / unpack to the device copies): w = g
+template <bool TO_W, bool TO_OUT>
+struct CopyOp {
+  static constexpr OpFlags F = {true, false, TO_W, TO_OUT, false, false, false, false, 0};
+  struct PT {};
+  __device__ __forceinline__ PT prep(float, float, float, float) const { return {}; }
+  template <typename T>
+  __device__ __forceinline__ void elem(const PT&, float& w, float g, float&, float&, float*) const {
+    w = g;
+  }
+};
+
+// out copies <- W section (fp32 master -> weight dtype), nothing else touched
+struct MasterToOutOp {
+  static constexpr OpFlags F = {false, true, false, true, false, false, false, false, 0};
+  struct PT {};
+  __device__ __forceinline__ PT prep(float, float, float, float) const { return {}; }
+  template <typename T>
+  __device__ __forceinline__ void elem(const PT&, float&, float, float&, float&, float*) const {}
+};
+
+template <class Op, class = void>
+struct HasPrepT { static constexpr bool value = false; };
+template <class Op>
+struct HasPrepT<Op, decltype((void)&Op::prep_t)> { static constexpr bool value = true; };
+
+template <class Op>
+__device__ __forceinline__ typename Op::PT op_prep(const Op& op, float lr, float wd, float a0,
+                                                   float a1, int t) {
+  if constexpr (HasPrepT<Op>::value) return op.prep_t(lr, wd, a0, a1, t);
+  else return op.prep(lr, wd, a0, a1);
+}
+
+// ------------------------------------------------------------------------------------------------
+// The generic chunk kernel.
+//   T   element type of gradients and of the `out` copies (float | __half)
+//   WT  element type of the W section (float master/weight, or T for pack/assign buckets)
+//   NG  1 = single gradient source, 0 = a.ngrad sources summed in CommCPU order
+// gscale (optional device scalar): global-norm clip factor, g = g*scale rounded in T like
+// `arr *= scale` in gluon/utils.py:155-156.
+// partials: [nchunks][nred] per-chunk reduction outputs (deterministic two-stage reduction, like
+// multi_sum_sq.cu's no-atomics design, NEWS.md:795).
+// ------------------------------------------------------------------------------------------------
+template <class Op, typename T, typename WT, int NG>
+__global__ void __launch_bounds__(kThreads, 2)
+mta_kernel(const MtaArgs a, const Op op, const float* __restrict__ gscale,
+           float* __restrict__ partials) {
+  constexpr OpFlags F = Op::F;
+  __shared__ float sred[2][kThreads / 32];
+  const int tid = threadIdx.x;
+  const float gs = (F.read_g && gscale != nullptr) ? *gscale : 1.0f;
+  const bool use_gs = F.read_g && gscale != nullptr;
+
+  for (int c = blockIdx.x; c < a.nchunks; c += gridDim.x) {
+    const Chunk ch = a.chunks[c];
+    const int t = ch.tensor;
+    const int64_t base = ch.off;
+    WT* const wp = reinterpret_cast<WT*>(sec(a, kSecW)[t]);
+    float* const s0p = reinterpret_cast<float*>(sec(a, kSecS0)[t]);
+    float* const s1p = reinterpret_cast<float*>(sec(a, kSecS1)[t]);
+    const float2 lrwd = *reinterpret_cast<const float2*>(&sec(a, kSecLrWd)[t]);
+    const float2 aux = *reinterpret_cast<const float2*>(&sec(a, kSecAux)[t]);
+    const typename Op::PT pt = op_prep(op, lrwd.x, lrwd.y, aux.x, aux.y, t);
+    float red[2] = {0.f, 0.f};
+
+    // 16-byte alignment (8 for a 2-byte type) of every array at this chunk's first element
+    uint64_t bits = 0;
+    const uint64_t o4 = static_cast<uint64_t>(base) * 4, oT = static_cast<uint64_t>(base) * sizeof(T),
+                   oW = static_cast<uint64_t>(base) * sizeof(WT);
+    constexpr uint64_t mT = sizeof(T) == 2 ? 2 : 1, mW = sizeof(WT) == 2 ? 2 : 1;
+    if (F.read_w || F.write_w) bits |= (reinterpret_cast<uint64_t>(wp) + oW) * mW;
+    if (F.read_s0 || F.write_s0) bits |= reinterpret_cast<uint64_t>(s0p) + o4;
+    if (F.read_s1 || F.write_s1) bits |= reinterpret_cast<uint64_t>(s1p) + o4;
+    if (F.read_g) {
+      const int ng = NG == 0 ? a.ngrad : 1;
+      for (int k = 0; k < ng; ++k) bits |= (sec_grad(a, k)[t] + oT) * mT;
+    }
+    if (F.write_out)
+      for (int k = 0; k < a.nout; ++k) bits |= (sec_out(a, k)[t] + oT) * mT;
+    const bool vec = (bits & 15) == 0;
+
+    if (vec) {
+      const int nvec = ch.len >> 2;
+      float w[kU][4], g[kU][4], s0[kU][4], s1[kU][4];
+#pragma unroll
+      for (int u = 0; u < kU; ++u) {
+        const int v = u * kThreads + tid;
+        if (v < nvec) {
+          const int64_t e = base + 4 * v;
+          if (F.read_g) grad4<T, NG>(a, t, e, g[u]);
+          if (F.read_w) ld4(wp + e, w[u]);
+          if (F.read_s0) ld4(s0p + e, s0[u]);
+          if (F.read_s1) ld4(s1p + e, s1[u]);
+        }
+      }
+#pragma unroll
+      for (int u = 0; u < kU; ++u) {
+        const int v = u * kThreads + tid;
+        if (v < nvec) {
+          const int64_t e = base + 4 * v;
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            if (use_gs) g[u][j] = round_to<T>(__fmul_rn(g[u][j], gs));
+            op.template elem<T>(pt, w[u][j], g[u][j], s0[u][j], s1[u][j], red);
+          }
+          if (F.write_s0) st4(s0p + e, s0[u]);
+          if (F.write_s1) st4(s1p + e, s1[u]);
+          if (F.write_w) st4(wp + e, w[u]);
+          if (F.write_out)
+            for (int k = 0; k < a.nout; ++k) st4(reinterpret_cast<T*>(sec_out(a, k)[t]) + e, w[u]);
+        }
+      }
+    }
+    // scalar path: the <4-element tail of a vector chunk, or the whole chunk when unaligned
+    for (int i = (vec ? (ch.len & ~3) : 0) + tid; i < ch.len; i += kThreads) {
+      const int64_t e = base + i;
+      float w = 0.f, g = 0.f, s0 = 0.f, s1 = 0.f;
+      if (F.read_g) g = grad1<T, NG>(a, t, e);
+      if (use_gs) g = round_to<T>(__fmul_rn(g, gs));
+      if (F.read_w) w = ld1(wp + e);
+      if (F.read_s0) s0 = s0p[e];
+      if (F.read_s1) s1 = s1p[e];
+      op.template elem<T>(pt, w, g, s0, s1, red);
+      if (F.write_s0) s0p[e] = s0;
+      if (F.write_s1) s1p[e] = s1;
+      if (F.write_w) st1(wp + e, w);
+      if (F.write_out)
+        for (int k = 0; k < a.nout; ++k) st1(reinterpret_cast<T*>(sec_out(a, k)[t]) + e, w);
+    }
+
+    if (F.nred > 0) {
+      // warp shuffle, then shared memory across the 8 warps; fixed order => run-to-run identical
+#pragma unroll
+      for (int r = 0; r < F.nred; ++r) {
+        float x = red[r];
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) x += __shfl_down_sync(0xffffffffu, x, o);
+        if ((tid & 31) == 0) sred[r][tid >> 5] = x;
+      }
+      __syncthreads();
+      if (tid < F.nred) {
+        float x = 0.f;
+#pragma unroll
+        for (int k = 0; k < kThreads / 32; ++k) x += sred[tid][k];
+        partials[static_cast<size_t>(c) * F.nred + tid] = x;
+      }
+      __syncthreads();
+    }
+  }
+}
+
+// second stage of the deterministic reduction: one warp per tensor sums that tensor's chunk
+// partials (chunks of a tensor are consecutive: [first[t], first[t+1])).  sums is [nred][nt];
+// accumulate != 0 adds to the existing value (used when a tensor list is processed in pieces).
+__global__ void reduce_partials_kernel(const float* __restrict__ partials,
+                                       const int* __restrict__ first, int nt, int nred,
+                                       float* __restrict__ sums) {
+  const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int lane = threadIdx.x & 31;
+  if (warp >= nt) return;
+  const int b = first[warp], e = first[warp + 1];
+  for (int r = 0; r < nred; ++r) {
+    float x = 0.f;
+    for (int c = b + lane; c < e; c += 32) x += partials[static_cast<size_t>(c) * nred + r];
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) x += __shfl_down_sync(0xffffffffu, x, o);
+    if (lane == 0) sums[static_cast<size_t>(r) * nt + warp] = x;
+  }
+}
+
+// LAMB trust ratio per tensor (multi_lamb.cc:92-104): sums = [sum w^2 | sum u^2], each [nt]
+__global__ void lamb_ratio_kernel(const float* __restrict__ sums, int nt, float lower, float upper,
+                                  float* __restrict__ ratio) {
+  const int t = blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= nt) return;
+  float r1 = __fsqrt_rn(sums[t]);
+  const float r2 = __fsqrt_rn(sums[nt + t]);
+  if (lower >= 0) r1 = fmaxf(r1, lower);
+  if (upper >= 0) r1 = fminf(r1, upper);
+  ratio[t] = (r1 == 0.0f || r2 == 0.0f) ? 1.0f : __fdiv_rn(r1, r2);
+}
+
+// clip_global_norm scalar (gluon/utils.py:149-154): out[0] = scale = min(max_norm/(norm+1e-8), 1),
+// out[1] = norm.  One block; per-tensor sums are added in a fixed tree order.
+__global__ void global_norm_kernel(const float* __restrict__ sums, int nt, float max_norm,
+                                   float* __restrict__ out) {
+  __shared__ float s[kThreads];
+  float x = 0.f;
+  for (int t = threadIdx.x; t < nt; t += kThreads) x += sums[t];
+  s[threadIdx.x] = x;
+  __syncthreads();
+  for (int o = kThreads / 2; o > 0; o >>= 1) {
+    if (threadIdx.x < o) s[threadIdx.x] += s[threadIdx.x + o];
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) {
+    const float norm = __fsqrt_rn(s[0]);
+    const float scale = __fdiv_rn(max_norm, __fadd_rn(norm, 1e-8f));
+    out[0] = fminf(scale, 1.0f);
+    out[1] = norm;
+  }
+}
+
+}  // namespace b200kv

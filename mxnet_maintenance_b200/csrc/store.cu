@@ -1,0 +1,650 @@
+// Dense part of the store.  Reference semantics: src/kvstore/kvstore_local.h:226-343 (init / push /
+// pull / pushpull / broadcast, grouping, key checks); the reduce + broadcast it replaces:
+// CommDevice::Reduce/Broadcast (src/kvstore/comm.h:503-616) and KVStoreNCCL::Reduce/Broadcast
+// (src/kvstore/kvstore_nccl.h:213-421).
+#include "store.h"
+
+#include <algorithm>
+#include <cmath>
+#include <cstring>
+
+#include "nccl_dl.h"
+
+namespace b200kv {
+
+int launch_cast(const void* src, int src_dtype, void* dst, int dst_dtype, int64_t n,
+                cudaStream_t stream);  // optim.cu
+
+namespace {
+
+int64_t align_up(int64_t x, int64_t a) { return (x + a - 1) / a * a; }
+
+struct Blob {
+  uint64_t* p;
+  int nt, ngrad, nout;
+  Blob(uint64_t* base, int nt_, int ng, int no) : p(base), nt(nt_), ngrad(ng), nout(no) {
+    std::memset(p, 0, words() * 8);
+  }
+  size_t words() const { return mta_blob_words(nt, ngrad, nout); }
+  void G(int k, int t, const void* ptr) { p[static_cast<size_t>(k) * nt + t] = reinterpret_cast<uint64_t>(ptr); }
+  void O(int k, int t, const void* ptr) { p[static_cast<size_t>(ngrad + k) * nt + t] = reinterpret_cast<uint64_t>(ptr); }
+  void S(int sec, int t, const void* ptr) {
+    p[static_cast<size_t>(ngrad + nout + sec) * nt + t] = reinterpret_cast<uint64_t>(ptr);
+  }
+  void F2(int sec, int t, float a, float b) {
+    float v[2] = {a, b};
+    std::memcpy(&p[static_cast<size_t>(ngrad + nout + sec) * nt + t], v, 8);
+  }
+};
+
+inline char* at(const DevBuf& b, int64_t elem, size_t esize) {
+  // may point outside the allocation for shard-relative arrays; only in-range chunks dereference it
+  return static_cast<char*>(b.p) + elem * static_cast<int64_t>(esize);
+}
+
+}  // namespace
+
+Store::Store(int device, int rank, int world) : device_(device), rank_(rank), world_(world) {
+  KV_CHECK(world >= 1 && rank >= 0 && rank < world, "invalid rank " << rank << " / world " << world);
+  int n = 0;
+  CUDA_OK(cudaGetDeviceCount(&n));
+  KV_CHECK(device >= 0 && device < n, "invalid CUDA device " << device << " (" << n << " visible)");
+  std::memset(&opt_, 0, sizeof(opt_));
+  opt_.kind = B200KV_OPT_NONE;
+  opt_.clip_global_norm = -1.f;
+  use_device();
+  gnorm_.reserve(2 * sizeof(float));
+}
+
+Store::~Store() {
+  cudaSetDevice(device_);
+  cudaStreamSynchronize(stream_);
+  if (comm_) NcclApi::get().CommDestroy(reinterpret_cast<ncclComm_t>(comm_));
+}
+
+void Store::use_device() { CUDA_OK(cudaSetDevice(device_)); }
+
+void Store::wait() {
+  use_device();
+  CUDA_OK(cudaStreamSynchronize(stream_));
+}
+
+void Store::comm_init(const char id[128]) {
+  use_device();
+  KV_CHECK(comm_ == nullptr, "communicator already initialised");
+  if (world_ == 1) return;
+  static_assert(sizeof(ncclUniqueId) == 128, "ncclUniqueId size");
+  ncclUniqueId uid;
+  std::memcpy(&uid, id, sizeof(uid));
+  ncclComm_t c;
+  NCCL_OK(NcclApi::get().CommInitRank(&c, world_, uid, rank_));
+  comm_ = reinterpret_cast<ncclComm*>(c);
+}
+
+void Store::barrier() {
+  use_device();
+  if (world_ > 1) {
+    KV_CHECK(comm_, "b200kv_comm_init has not been called");
+    NCCL_OK(NcclApi::get().AllReduce(gnorm_.p, gnorm_.p, 0, ncclFloat32, ncclSum,
+                                     reinterpret_cast<ncclComm_t>(comm_), stream_));
+  }
+  CUDA_OK(cudaStreamSynchronize(stream_));
+}
+
+// ---- keys ----------------------------------------------------------------------------------------
+void Store::check_key_type(bool is_str) {
+  // kvstore_local.h:322-325: a store uses either int or string keys, never both
+  const int t = is_str ? 1 : 0;
+  if (key_type_ < 0) key_type_ = t;
+  KV_CHECK(key_type_ == t, "inconsistent key types: mixing int and string keys is not allowed");
+}
+
+void Store::lookup_keys(int num, const char* const* names, bool create, int* out) {
+  check_key_type(true);
+  for (int i = 0; i < num; ++i) {
+    const std::string s(names[i]);
+    auto it = str_keys_.find(s);
+    if (it == str_keys_.end()) {
+      KV_CHECK(create, "key " << s << " has not been initialized");
+      const int k = static_cast<int>(str_keys_.size());
+      it = str_keys_.emplace(s, k).first;
+    }
+    out[i] = it->second;
+  }
+}
+
+KeyInfo& Store::info(int key) {
+  auto it = keys_.find(key);
+  KV_CHECK(it != keys_.end(), "key " << key << " has not been initialized");
+  return it->second;
+}
+
+void Store::init(int num, const int* keys, DLManagedTensor* const* vals) {
+  use_device();
+  if (key_type_ < 0) key_type_ = 0;
+  for (int i = 0; i < num; ++i) {
+    KV_CHECK(keys_.find(keys[i]) == keys_.end() && rsp_.find(keys[i]) == rsp_.end(),
+             "duplicate init of key " << keys[i]);   // kvstore_local.h:229-232
+    const TensorView v = view_of(vals[i], device_, "init value");
+    KV_CHECK(v.dtype == kF32 || v.dtype == kF16, "init: only float32/float16 values are supported");
+    KeyInfo k;
+    k.key = keys[i];
+    k.dtype = v.dtype;
+    k.size = v.numel;
+    k.staged.reset(new DevBuf());
+    const size_t bytes = static_cast<size_t>(v.numel) * dtype_size(v.dtype);
+    k.staged->reserve(bytes ? bytes : 16);
+    if (bytes)
+      CUDA_OK(cudaMemcpyAsync(k.staged->p, v.data, bytes, cudaMemcpyDeviceToDevice, stream_));
+    if (world_ > 1 && bytes) {  // every rank starts from rank 0's value
+      KV_CHECK(comm_, "b200kv_comm_init has not been called");
+      NCCL_OK(NcclApi::get().Broadcast(k.staged->p, k.staged->p, v.numel, nccl_type(v.dtype), 0,
+                                       reinterpret_cast<ncclComm_t>(comm_), stream_));
+    }
+    keys_.emplace(keys[i], std::move(k));
+    unsealed_.push_back(keys[i]);
+  }
+}
+
+// Move every staged key into a new flat segment per dtype.
+void Store::seal() {
+  if (unsealed_.empty()) return;
+  for (int dt : {static_cast<int>(kF32), static_cast<int>(kF16)}) {
+    std::vector<int> ks;
+    for (int k : unsealed_)
+      if (keys_[k].dtype == dt) ks.push_back(k);
+    if (ks.empty()) continue;
+    std::unique_ptr<Segment> s(new Segment());
+    s->dtype = dt;
+    int64_t off = 0;
+    for (int k : ks) {
+      KeyInfo& ki = keys_[k];
+      ki.off = off;
+      ki.seg = static_cast<int>(segs_.size());
+      off = align_up(off + ki.size, kAlignElems);
+    }
+    s->total = align_up(std::max<int64_t>(off, kAlignElems), static_cast<int64_t>(world_) * kAlignElems);
+    s->slice = s->total / world_;
+    s->keys = ks;
+    const size_t es = dtype_size(dt);
+    s->wbuf.reserve(static_cast<size_t>(s->total) * es);
+    CUDA_OK(cudaMemsetAsync(s->wbuf.p, 0, static_cast<size_t>(s->total) * es, stream_));
+    for (int k : ks) {
+      KeyInfo& ki = keys_[k];
+      if (ki.size)
+        CUDA_OK(cudaMemcpyAsync(at(s->wbuf, ki.off, es), ki.staged->p, static_cast<size_t>(ki.size) * es,
+                                cudaMemcpyDeviceToDevice, stream_));
+    }
+    // staged buffers are freed after the copies have run
+    CUDA_OK(cudaStreamSynchronize(stream_));
+    for (int k : ks) keys_[k].staged.reset();
+    segs_.push_back(std::move(s));
+  }
+  unsealed_.clear();
+}
+
+// ---- optimizer -----------------------------------------------------------------------------------
+void Store::set_optimizer(const b200kv_optimizer& o) {
+  use_device();
+  KV_CHECK(o.kind >= B200KV_OPT_NONE && o.kind <= B200KV_OPT_LAMB, "unknown optimizer kind " << o.kind);
+  const bool had_mom = opt_.kind == B200KV_OPT_SGD && opt_.momentum != 0.f;
+  const bool has_mom = o.kind == B200KV_OPT_SGD && o.momentum != 0.f;
+  const bool reset = o.kind != opt_.kind || o.multi_precision != opt_.multi_precision || had_mom != has_mom;
+  if (reset) {
+    for (auto& sp : segs_) {
+      Segment& s = *sp;
+      if (s.w_stale) {  // the master is authoritative: materialise the stored fp16 value first
+        launches_ += launch_cast(s.master.p, kF32, s.wbuf.p, kF16, s.total, stream_);
+        s.w_stale = false;
+      }
+      CUDA_OK(cudaStreamSynchronize(stream_));
+      s.master.release(); s.s0.release(); s.s1.release();
+      s.has_master = s.has_s0 = s.has_s1 = false;
+      s.state_len = 0;
+    }
+  }
+  opt_ = o;
+  sc_.momentum = o.momentum; sc_.beta1 = o.beta1; sc_.beta2 = o.beta2; sc_.eps = o.epsilon;
+  sc_.rescale = o.rescale_grad; sc_.clip = o.clip_gradient; sc_.lower = o.lower_bound;
+  sc_.upper = o.upper_bound; sc_.bias_correction = o.bias_correction;
+}
+
+void Store::set_hyper(int num, const int* keys, const float* lrs, const float* wds, const int* steps) {
+  for (int i = 0; i < num; ++i) {
+    auto it = keys_.find(keys[i]);
+    if (it != keys_.end()) {
+      if (lrs) it->second.lr = lrs[i];
+      if (wds) it->second.wd = wds[i];
+      if (steps) it->second.step = steps[i];
+      continue;
+    }
+    KV_CHECK(rsp_.find(keys[i]) != rsp_.end(), "key " << keys[i] << " has not been initialized");
+    set_hyper_rsp(keys[i], lrs ? lrs[i] : NAN, wds ? wds[i] : NAN, steps ? steps[i] : -1);
+  }
+}
+
+// States are created at the first update from the stored weight, as Updater.__call__ does
+// (python/mxnet/optimizer/optimizer.py:2096-2098); they cover only this rank's shard when world > 1.
+void Store::ensure_states(Segment& s) {
+  const bool want_s0 = (opt_.kind == B200KV_OPT_SGD && opt_.momentum != 0.f) ||
+                       opt_.kind == B200KV_OPT_ADAM || opt_.kind == B200KV_OPT_LAMB;
+  const bool want_s1 = opt_.kind == B200KV_OPT_ADAM || opt_.kind == B200KV_OPT_LAMB;
+  const bool want_master = use_mp(s);
+  if (s.state_len == 0) {
+    s.state_begin = world_ == 1 ? 0 : static_cast<int64_t>(rank_) * s.slice;
+    s.state_len = world_ == 1 ? s.total : s.slice;
+  }
+  const size_t bytes = static_cast<size_t>(s.state_len) * 4;
+  if (want_s0 && !s.has_s0) {
+    s.s0.reserve(bytes);
+    CUDA_OK(cudaMemsetAsync(s.s0.p, 0, bytes, stream_));
+    s.has_s0 = true;
+  }
+  if (want_s1 && !s.has_s1) {
+    s.s1.reserve(bytes);
+    CUDA_OK(cudaMemsetAsync(s.s1.p, 0, bytes, stream_));
+    s.has_s1 = true;
+  }
+  if (want_master && !s.has_master) {
+    s.master.reserve(bytes);
+    launches_ += launch_cast(at(s.wbuf, s.state_begin, 2), kF16, s.master.p, kF32, s.state_len, stream_);
+    s.has_master = true;
+  }
+}
+
+// ---- plans ---------------------------------------------------------------------------------------
+DensePlan& Store::plan_for(int seg, const std::vector<int>& keys, int ngrad, int nout) {
+  std::string id = std::to_string(seg) + ":" + std::to_string(ngrad) + ":" + std::to_string(nout) + ":";
+  id.reserve(id.size() + keys.size() * 6);
+  for (int k : keys) { id += std::to_string(k); id += ','; }
+  auto it = plans_.find(id);
+  if (it != plans_.end()) return *it->second;
+
+  std::unique_ptr<DensePlan> p(new DensePlan());
+  Segment& s = *segs_[seg];
+  p->keys = keys;
+  p->seg = seg;
+  p->ngrad = ngrad;
+  p->nout = nout;
+  p->full_segment = keys.size() == s.keys.size();
+  const int nt = static_cast<int>(keys.size());
+  std::vector<int64_t> b(nt, 0), e(nt), sb(nt), se(nt);
+  const int64_t lo = static_cast<int64_t>(rank_) * s.slice, hi = lo + s.slice;
+  for (int t = 0; t < nt; ++t) {
+    const KeyInfo& ki = keys_[keys[t]];
+    e[t] = ki.size;
+    // shard range relative to the tensor's first element
+    sb[t] = std::min(std::max(lo - ki.off, int64_t(0)), ki.size);
+    se[t] = std::max(std::min(hi - ki.off, ki.size), sb[t]);
+    if (world_ > 1)
+      for (int r = 0; r < world_; ++r) {
+        const int64_t plo = std::max(ki.off, r * s.slice), phi = std::min(ki.off + ki.size, (r + 1) * s.slice);
+        if (plo < phi) p->pieces.push_back({plo, phi - plo, r});
+      }
+  }
+  p->full.build(b, e);
+  if (world_ > 1) p->shard.build(sb, se);
+  const int maxc = std::max(p->full.nchunks, p->shard.nchunks);
+  p->partials.reserve(sizeof(float) * 2 * static_cast<size_t>(std::max(maxc, 1)));
+  p->sums.reserve(sizeof(float) * (3 * static_cast<size_t>(nt) + 4));
+  DensePlan& ref = *p;
+  plans_.emplace(id, std::move(p));
+  return ref;
+}
+
+// ---- the update sequence on a chunk list -----------------------------------------------------------
+const float* Store::global_norm_scale(DensePlan& p, const ChunkPlan& cp, const MtaCall& gcall) {
+  // clip_global_norm (python/mxnet/gluon/utils.py:122-161) on the merged gradients of this push
+  MtaCall c = gcall;
+  c.plan = &cp;
+  float* partials = p.partials.as<float>();
+  float* sums = p.sums.as<float>();
+  launches_ += launch_sumsq(c, partials);
+  launches_ += launch_reduce_partials(partials, cp, 1, sums, stream_);
+  if (world_ > 1)
+    NCCL_OK(NcclApi::get().AllReduce(sums, sums, c.nt, ncclFloat32, ncclSum,
+                                     reinterpret_cast<ncclComm_t>(comm_), stream_));
+  launches_ += launch_global_norm(sums, c.nt, opt_.clip_global_norm, gnorm_.as<float>(), stream_);
+  gnorm_valid_ = true;
+  return gnorm_.as<float>();
+}
+
+void Store::update_chunks(DensePlan& p, const ChunkPlan& cp, const MtaCall& call, const float* gscale) {
+  MtaCall c = call;
+  c.plan = &cp;
+  switch (opt_.kind) {
+    case B200KV_OPT_SGD:
+      launches_ += launch_sgd(c, opt_.momentum != 0.f, sc_, gscale);
+      break;
+    case B200KV_OPT_ADAM:
+      launches_ += launch_adam(c, sc_, gscale);
+      break;
+    case B200KV_OPT_LAMB: {
+      float* partials = p.partials.as<float>();
+      float* sums = p.sums.as<float>();
+      float* ratio = sums + 2 * static_cast<size_t>(c.nt);
+      launches_ += launch_lamb1(c, sc_, gscale, partials);
+      launches_ += launch_reduce_partials(partials, cp, 2, sums, stream_);
+      if (world_ > 1)  // per-tensor norms span shards: one tiny all-reduce between the two passes
+        NCCL_OK(NcclApi::get().AllReduce(sums, sums, 2 * static_cast<size_t>(c.nt), ncclFloat32, ncclSum,
+                                         reinterpret_cast<ncclComm_t>(comm_), stream_));
+      launches_ += launch_lamb_ratio(sums, c.nt, sc_.lower, sc_.upper, ratio, stream_);
+      launches_ += launch_lamb2(c, sc_, ratio);
+      break;
+    }
+    default:
+      KV_CHECK(false, "no optimizer set");
+  }
+}
+
+float Store::last_global_norm() {
+  use_device();
+  KV_CHECK(gnorm_valid_, "no push with clip_global_norm has run yet");
+  float h[2];
+  CUDA_OK(cudaMemcpyAsync(h, gnorm_.p, sizeof(h), cudaMemcpyDeviceToHost, stream_));
+  CUDA_OK(cudaStreamSynchronize(stream_));
+  return h[1];
+}
+
+// ---- one class of keys (same segment, same number of value / out copies) ---------------------------
+void Store::run_class(Mode mode, DensePlan& p, const std::vector<const Entry*>& ents) {
+  Segment& s = *segs_[p.seg];
+  const int nt = static_cast<int>(p.keys.size());
+  const size_t es = dtype_size(s.dtype);
+  const bool push = (mode & kPush) != 0, pull = (mode & kPull) != 0;
+  const bool mp = has_opt() && use_mp(s);
+  if (push && has_opt()) {
+    KV_CHECK(!(s.dtype == kF16 && !opt_.multi_precision),
+             "float16 weights need multi_precision=True (pure fp16 optimizer state is not supported)");
+    ensure_states(s);
+  }
+  NcclApi* nccl = world_ > 1 ? &NcclApi::get() : nullptr;
+  ncclComm_t comm = reinterpret_cast<ncclComm_t>(comm_);
+  if (world_ > 1) KV_CHECK(comm_, "b200kv_comm_init has not been called");
+
+  // carve all tables of this call out of one ring slot
+  const int ng = push ? p.ngrad : 1, no = pull ? p.nout : 0;
+  // sharded update (world > 1): one gradient source (the reduced bucket); the fp16 weight shard
+  // for the all-gather is its single "out" copy in multi-precision mode
+  const int upd_ng = world_ > 1 ? 1 : ng, upd_no = world_ > 1 ? (mp ? 1 : 0) : no;
+  const size_t w_pack = mta_blob_words(nt, ng, 0), w_upd = mta_blob_words(nt, upd_ng, upd_no),
+               w_unpack = mta_blob_words(nt, 1, no);
+  uint64_t* host = ring_.begin((w_pack + w_upd + w_unpack) * 8);
+  const uint64_t* dev = nullptr;  // set after commit; offsets are fixed now
+  const size_t o_pack = 0, o_upd = w_pack, o_unpack = w_pack + w_upd;
+
+  MtaCall base;
+  base.nt = nt;
+  base.dtype = s.dtype;
+  base.stream = stream_;
+  base.device = device_;
+
+  auto fill_update_scalars = [&](Blob& b) {
+    for (int t = 0; t < nt; ++t) {
+      const KeyInfo& ki = keys_[p.keys[t]];
+      b.S(kSecW, t, mp ? at(s.master, ki.off - s.state_begin, 4) : at(s.wbuf, ki.off, 4));
+      if (s.has_s0) b.S(kSecS0, t, at(s.s0, ki.off - s.state_begin, 4));
+      if (s.has_s1) b.S(kSecS1, t, at(s.s1, ki.off - s.state_begin, 4));
+      b.F2(kSecLrWd, t, ki.lr, ki.wd);
+      if (opt_.kind == B200KV_OPT_LAMB) {
+        // 1 - beta^t with the host's powf in fp32, as MultiLAMBKernelStep1 does per element
+        // (multi_lamb.cc:59-67)
+        const float tf = static_cast<float>(ki.step);
+        b.F2(kSecAux, t, 1.0f - powf(opt_.beta1, tf), 1.0f - powf(opt_.beta2, tf));
+      }
+    }
+  };
+
+  if (world_ == 1) {
+    if (push) {
+      Blob b(host + o_upd, nt, ng, no);
+      for (int t = 0; t < nt; ++t) {
+        for (int k = 0; k < ng; ++k) b.G(k, t, ents[t]->vals[k].data);
+        for (int k = 0; k < no; ++k) b.O(k, t, ents[t]->outs[k].data);
+      }
+      if (has_opt()) fill_update_scalars(b);
+      else for (int t = 0; t < nt; ++t) b.S(kSecW, t, at(s.wbuf, keys_[p.keys[t]].off, es));
+      dev = ring_.commit(stream_);
+      MtaCall c = base;
+      c.blob = dev + o_upd; c.ngrad = ng; c.nout = no; c.plan = &p.full;
+      if (has_opt()) {
+        const float* gscale = opt_.clip_global_norm >= 0.f ? global_norm_scale(p, p.full, c) : nullptr;
+        update_chunks(p, p.full, c, gscale);
+        if (mp) s.w_stale = true;
+      } else {
+        // no updater: the merged value replaces the stored one (kvstore_local.h:268-274)
+        launches_ += launch_copy(c, true, no > 0);
+      }
+    } else {  // pull only
+      Blob b(host + o_unpack, nt, 1, no);
+      for (int t = 0; t < nt; ++t) {
+        const KeyInfo& ki = keys_[p.keys[t]];
+        b.G(0, t, at(s.wbuf, ki.off, es));
+        b.S(kSecW, t, s.w_stale ? at(s.master, ki.off - s.state_begin, 4) : nullptr);
+        for (int k = 0; k < no; ++k) b.O(k, t, ents[t]->outs[k].data);
+      }
+      dev = ring_.commit(stream_);
+      MtaCall c = base;
+      c.blob = dev + o_unpack; c.ngrad = 1; c.nout = no; c.plan = &p.full;
+      if (s.w_stale) launches_ += launch_master_to_out(c);
+      else launches_ += launch_copy(c, false, true);
+    }
+    ring_.end(stream_);
+    return;
+  }
+
+  // ---------------- world > 1: pack -> reduce-scatter -> sharded update -> all-gather -> unpack
+  if (s.gbuf.p == nullptr && push) {
+    s.gbuf.reserve(static_cast<size_t>(s.total) * es);
+    CUDA_OK(cudaMemsetAsync(s.gbuf.p, 0, static_cast<size_t>(s.total) * es, stream_));
+  }
+  if (push) {
+    Blob b(host + o_pack, nt, ng, 0);
+    for (int t = 0; t < nt; ++t) {
+      for (int k = 0; k < ng; ++k) b.G(k, t, ents[t]->vals[k].data);
+      b.S(kSecW, t, at(s.gbuf, keys_[p.keys[t]].off, es));
+    }
+    if (has_opt()) {
+      Blob u(host + o_upd, nt, upd_ng, upd_no);
+      for (int t = 0; t < nt; ++t) {
+        const KeyInfo& ki = keys_[p.keys[t]];
+        u.G(0, t, at(s.gbuf, ki.off, es));
+        if (mp) u.O(0, t, at(s.wbuf, ki.off, es));
+      }
+      fill_update_scalars(u);
+    }
+  }
+  if (pull) {
+    Blob b(host + o_unpack, nt, 1, no);
+    for (int t = 0; t < nt; ++t) {
+      b.G(0, t, at(s.wbuf, keys_[p.keys[t]].off, es));
+      for (int k = 0; k < no; ++k) b.O(k, t, ents[t]->outs[k].data);
+    }
+  }
+  dev = ring_.commit(stream_);
+  const ncclDataType_t nt_type = nccl_type(s.dtype);
+  if (push) {
+    MtaCall c = base;
+    c.blob = dev + o_pack; c.ngrad = ng; c.nout = 0; c.plan = &p.full;
+    launches_ += launch_copy(c, true, false);   // user gradients (local copies summed) -> fusion bucket
+    if (has_opt()) {
+      if (p.full_segment) {
+        NCCL_OK(nccl->ReduceScatter(s.gbuf.p, at(s.gbuf, rank_ * s.slice, es), s.slice, nt_type, ncclSum,
+                                    comm, stream_));
+      } else {
+        NCCL_OK(nccl->GroupStart());
+        for (const auto& pc : p.pieces)
+          NCCL_OK(nccl->Reduce(at(s.gbuf, pc.off, es), at(s.gbuf, pc.off, es), pc.len, nt_type, ncclSum,
+                               pc.root, comm, stream_));
+        NCCL_OK(nccl->GroupEnd());
+      }
+      MtaCall u = base;
+      u.blob = dev + o_upd; u.ngrad = upd_ng; u.nout = upd_no; u.plan = &p.shard;
+      const float* gscale = opt_.clip_global_norm >= 0.f ? global_norm_scale(p, p.shard, u) : nullptr;
+      update_chunks(p, p.shard, u, gscale);
+      if (p.full_segment) {
+        NCCL_OK(nccl->AllGather(at(s.wbuf, rank_ * s.slice, es), s.wbuf.p, s.slice, nt_type, comm, stream_));
+      } else {
+        NCCL_OK(nccl->GroupStart());
+        for (const auto& pc : p.pieces)
+          NCCL_OK(nccl->Broadcast(at(s.wbuf, pc.off, es), at(s.wbuf, pc.off, es), pc.len, nt_type, pc.root,
+                                  comm, stream_));
+        NCCL_OK(nccl->GroupEnd());
+      }
+    } else {
+      // no updater: all-reduce the merged gradients straight into the stored values
+      if (p.full_segment) {
+        NCCL_OK(nccl->AllReduce(s.gbuf.p, s.wbuf.p, s.total, nt_type, ncclSum, comm, stream_));
+      } else {
+        NCCL_OK(nccl->GroupStart());
+        for (int t = 0; t < nt; ++t) {
+          const KeyInfo& ki = keys_[p.keys[t]];
+          NCCL_OK(nccl->AllReduce(at(s.gbuf, ki.off, es), at(s.wbuf, ki.off, es), ki.size, nt_type, ncclSum,
+                                  comm, stream_));
+        }
+        NCCL_OK(nccl->GroupEnd());
+      }
+    }
+  }
+  if (pull) {
+    MtaCall c = base;
+    c.blob = dev + o_unpack; c.ngrad = 1; c.nout = no; c.plan = &p.full;
+    launches_ += launch_copy(c, false, true);
+  }
+  ring_.end(stream_);
+}
+
+void Store::pull_staged(const Entry& e) {
+  const KeyInfo& ki = keys_[e.key];
+  const size_t bytes = static_cast<size_t>(ki.size) * dtype_size(ki.dtype);
+  for (const auto& o : e.outs)
+    if (bytes) CUDA_OK(cudaMemcpyAsync(o.data, ki.staged->p, bytes, cudaMemcpyDeviceToDevice, stream_));
+}
+
+void Store::dense(Mode mode, int vnum, const int* vkeys, DLManagedTensor* const* vals, int onum,
+                  const int* okeys, DLManagedTensor* const* outs) {
+  use_device();
+  // GroupKVPairs (kvstore_local.h:417-447): entries with the same key are device copies of it
+  std::vector<Entry> ents;
+  std::unordered_map<int, size_t> where;
+  auto entry = [&](int key) -> Entry& {
+    auto it = where.find(key);
+    if (it == where.end()) {
+      it = where.emplace(key, ents.size()).first;
+      ents.push_back(Entry{key, {}, {}});
+    }
+    return ents[it->second];
+  };
+  auto check = [&](const TensorView& v, int key, const char* what) {
+    const KeyInfo& ki = info(key);
+    KV_CHECK(!ki.rsp, what << ": key " << key << " is row_sparse; use the row-sparse entry points");
+    KV_CHECK(v.dtype == ki.dtype, what << ": dtype mismatch for key " << key);
+    KV_CHECK(v.numel == ki.size, what << ": key " << key << " holds " << ki.size << " elements, got "
+                                      << v.numel);
+  };
+  if (mode & kPush)
+    for (int i = 0; i < vnum; ++i) {
+      KV_CHECK(rsp_.find(vkeys[i]) == rsp_.end(), "key " << vkeys[i] << " is row_sparse; use b200kv_push_rsp");
+      const TensorView v = view_of(vals[i], device_, "push value");
+      check(v, vkeys[i], "push");
+      entry(vkeys[i]).vals.push_back(v);
+    }
+  if (mode & kPull)
+    for (int i = 0; i < onum; ++i) {
+      KV_CHECK(rsp_.find(okeys[i]) == rsp_.end(), "key " << okeys[i] << " is row_sparse; use b200kv_row_sparse_pull");
+      const TensorView v = view_of(outs[i], device_, "pull out");
+      check(v, okeys[i], "pull");
+      entry(okeys[i]).outs.push_back(v);
+    }
+  bool need_seal = false;
+  for (const Entry& e : ents)
+    if (!e.vals.empty() && keys_[e.key].seg < 0) need_seal = true;
+  if (need_seal) seal();
+
+  // classes: (pushes?, segment, #vals, #outs) -> entries sorted by flat offset
+  struct Cls { int mode, seg, ng, no; std::vector<const Entry*> ents; };
+  std::vector<Cls> classes;
+  for (const Entry& e : ents) {
+    const KeyInfo& ki = keys_[e.key];
+    if (ki.seg < 0) {  // only pulled, never pushed yet: serve from the staged init value
+      pull_staged(e);
+      continue;
+    }
+    const int m = (e.vals.empty() ? 0 : kPush) | (e.outs.empty() ? 0 : kPull);
+    const int ng = static_cast<int>(e.vals.size()), no = static_cast<int>(e.outs.size());
+    KV_CHECK(ng <= kMaxCopies && no <= kMaxCopies, "at most " << kMaxCopies << " device-local copies per key");
+    Cls* c = nullptr;
+    for (auto& x : classes)
+      if (x.mode == m && x.seg == ki.seg && x.ng == ng && x.no == no) c = &x;
+    if (!c) {
+      classes.push_back(Cls{m, ki.seg, ng, no, {}});
+      c = &classes.back();
+    }
+    c->ents.push_back(&e);
+  }
+  // pushes first, then pure pulls (PushPullImpl = PushImpl; PullImpl, kvstore_local.h:336-343)
+  for (int pass = 0; pass < 2; ++pass)
+    for (auto& c : classes) {
+      if ((pass == 0) != ((c.mode & kPush) != 0)) continue;
+      std::sort(c.ents.begin(), c.ents.end(), [&](const Entry* a, const Entry* b) {
+        return keys_[a->key].off < keys_[b->key].off;
+      });
+      std::vector<int> ks;
+      ks.reserve(c.ents.size());
+      for (const Entry* e : c.ents) ks.push_back(e->key);
+      DensePlan& p = plan_for(c.seg, ks, c.ng, c.no);
+      run_class(static_cast<Mode>(c.mode), p, c.ents);
+    }
+}
+
+// ---- optimizer state access (checkpointing) --------------------------------------------------------
+void Store::get_state(int key, int which, DLManagedTensor* out, int* present) {
+  use_device();
+  const KeyInfo& ki = info(key);
+  *present = 0;
+  if (ki.seg < 0) return;
+  Segment& s = *segs_[ki.seg];
+  const DevBuf* src = which == 0 ? (s.has_s0 ? &s.s0 : nullptr)
+                    : which == 1 ? (s.has_s1 ? &s.s1 : nullptr)
+                    : which == 2 ? (s.has_master ? &s.master : nullptr) : nullptr;
+  KV_CHECK(which >= 0 && which <= 2, "state selector must be 0, 1 or 2");
+  if (!src) return;
+  const TensorView v = view_of(out, device_, "state out");
+  KV_CHECK(v.dtype == kF32 && v.numel == ki.size, "state out must be float32 with " << ki.size << " elements");
+  const int64_t lo = std::max(ki.off, s.state_begin), hi = std::min(ki.off + ki.size, s.state_begin + s.state_len);
+  if (world_ > 1) CUDA_OK(cudaMemsetAsync(v.data, 0, static_cast<size_t>(ki.size) * 4, stream_));
+  if (lo < hi)
+    CUDA_OK(cudaMemcpyAsync(static_cast<float*>(v.data) + (lo - ki.off), at(*src, lo - s.state_begin, 4),
+                            static_cast<size_t>(hi - lo) * 4, cudaMemcpyDeviceToDevice, stream_));
+  if (world_ > 1)  // every rank contributes its shard; the others hold zeros
+    NCCL_OK(NcclApi::get().AllReduce(v.data, v.data, ki.size, ncclFloat32, ncclSum,
+                                     reinterpret_cast<ncclComm_t>(comm_), stream_));
+  *present = 1;
+}
+
+void Store::set_state(int key, int which, DLManagedTensor* in) {
+  use_device();
+  const KeyInfo& ki = info(key);
+  KV_CHECK(which >= 0 && which <= 2, "state selector must be 0, 1 or 2");
+  KV_CHECK(has_opt(), "set_state needs an optimizer");
+  if (ki.seg < 0) seal();
+  Segment& s = *segs_[keys_[key].seg];
+  ensure_states(s);
+  DevBuf* dst = which == 0 ? (s.has_s0 ? &s.s0 : nullptr)
+              : which == 1 ? (s.has_s1 ? &s.s1 : nullptr) : (s.has_master ? &s.master : nullptr);
+  KV_CHECK(dst, "the current optimizer keeps no such state");
+  const TensorView v = view_of(in, device_, "state in");
+  KV_CHECK(v.dtype == kF32 && v.numel == ki.size, "state must be float32 with " << ki.size << " elements");
+  const int64_t lo = std::max(ki.off, s.state_begin), hi = std::min(ki.off + ki.size, s.state_begin + s.state_len);
+  if (lo < hi)
+    CUDA_OK(cudaMemcpyAsync(at(*dst, lo - s.state_begin, 4), static_cast<const float*>(v.data) + (lo - ki.off),
+                            static_cast<size_t>(hi - lo) * 4, cudaMemcpyDeviceToDevice, stream_));
+  if (which == 2) {
+    // the fp16 stored value follows its master
+    if (world_ == 1) s.w_stale = true;
+    else if (lo < hi)
+      launches_ += launch_cast(at(*dst, lo - s.state_begin, 4), kF32, at(s.wbuf, lo, 2), kF16, hi - lo, stream_);
+  }
+}
+
+}  // namespace b200kv

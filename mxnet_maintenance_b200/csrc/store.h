@@ -1,0 +1,132 @@
+// The store object behind the C ABI: KVStoreLocal's bookkeeping (src/kvstore/kvstore_local.h:94-343)
+// re-designed around flat per-dtype segments in HBM so that one push of a whole model is a handful
+// of launches:  [pack -> reduce-scatter ->] fused update on the rank's shard [-> all-gather -> unpack].
+#pragma once
+#include <map>
+#include <memory>
+#include <string>
+#include <unordered_map>
+#include <vector>
+
+#include "common.h"
+#include "launch.h"
+
+struct ncclComm;
+
+namespace b200kv {
+
+constexpr int64_t kAlignElems = 64;  // every key starts on a 64-element (>=128 B) boundary
+
+struct KeyInfo {
+  int key = 0;
+  bool rsp = false;
+  int dtype = kF32;
+  int64_t size = 0;
+  int seg = -1;        // segment index once sealed into a flat segment
+  int64_t off = 0;     // element offset inside the segment
+  std::unique_ptr<DevBuf> staged;  // value between init and the first push
+  float lr = 0.01f, wd = 0.f;
+  int step = 0;
+};
+
+// A flat, per-dtype slab of keys.  Element offsets are shared by every parallel array.
+struct Segment {
+  int dtype = kF32;
+  int64_t total = 0;   // elements, padded to world * kAlignElems
+  int64_t slice = 0;   // total / world: rank r owns [r*slice, (r+1)*slice)
+  std::vector<int> keys;
+  DevBuf wbuf;         // stored values, `dtype`, [total]
+  DevBuf gbuf;         // gradient fusion bucket, `dtype`, [total] (world > 1)
+  DevBuf master;       // fp32 master weights (multi-precision), [state_len]
+  DevBuf s0, s1;       // fp32 optimizer state, [state_len]
+  int64_t state_begin = 0, state_len = 0;  // element range the state arrays cover
+  bool has_s0 = false, has_s1 = false, has_master = false;
+  bool w_stale = false;  // world == 1 && master: wbuf lags behind master (pull casts the master)
+};
+
+struct DensePlan {
+  std::vector<int> keys;   // sorted by flat offset
+  int seg = -1, ngrad = 0, nout = 0;
+  bool full_segment = false;
+  ChunkPlan full, shard;
+  DevBuf partials;         // 2 floats per chunk
+  DevBuf sums;             // sums[2*nt] | ratio[nt] | gnorm[2]
+  struct Piece { int64_t off, len; int root; };
+  std::vector<Piece> pieces;   // (key range) x (owner slice), world > 1 partial path
+};
+
+struct RspKey;  // rsp.cu
+
+class Store {
+ public:
+  Store(int device, int rank, int world);
+  ~Store();
+
+  void set_stream(cudaStream_t s) { stream_ = s; }
+  void wait();
+  void comm_init(const char id[128]);
+  void lookup_keys(int num, const char* const* names, bool create, int* out);
+
+  void init(int num, const int* keys, DLManagedTensor* const* vals);
+  enum Mode { kPush = 1, kPull = 2, kPushPull = 3 };
+  void dense(Mode mode, int vnum, const int* vkeys, DLManagedTensor* const* vals, int onum,
+             const int* okeys, DLManagedTensor* const* outs);
+  void set_optimizer(const b200kv_optimizer& opt);
+  void set_hyper(int num, const int* keys, const float* lrs, const float* wds, const int* steps);
+  float last_global_norm();
+  void get_state(int key, int which, DLManagedTensor* out, int* present);
+  void set_state(int key, int which, DLManagedTensor* in);
+  void barrier();
+
+  // row sparse (rsp.cu)
+  void init_rsp(int key, DLManagedTensor* dense_value);
+  void push_rsp(int key, int ncopies, DLManagedTensor* const* idx, DLManagedTensor* const* val);
+  int64_t rsp_merged_size(int key);
+  void rsp_merged_copy(int key, DLManagedTensor* out_idx, DLManagedTensor* out_val);
+  int64_t row_sparse_pull(int key, DLManagedTensor* row_ids, DLManagedTensor* out_idx,
+                          DLManagedTensor* out_val);
+
+  int rank() const { return rank_; }
+  int world() const { return world_; }
+  int64_t launches() const { return launches_; }
+  const char* type() const { return "b200"; }
+
+ private:
+  friend struct RspKey;
+  struct Entry {
+    int key;
+    std::vector<TensorView> vals, outs;
+  };
+  KeyInfo& info(int key);
+  void use_device();
+  void check_key_type(bool is_str);
+  void seal();
+  void ensure_states(Segment& s);
+  DensePlan& plan_for(int seg, const std::vector<int>& keys, int ngrad, int nout);
+  void run_class(Mode mode, DensePlan& p, const std::vector<const Entry*>& ents);
+  void pull_staged(const Entry& e);
+  void update_chunks(DensePlan& p, const ChunkPlan& cp, const MtaCall& call, const float* gscale);
+  const float* global_norm_scale(DensePlan& p, const ChunkPlan& cp, const MtaCall& gcall);
+  void set_hyper_rsp(int key, float lr, float wd, int step);
+  bool has_opt() const { return opt_.kind != B200KV_OPT_NONE; }
+  bool use_mp(const Segment& s) const { return s.dtype == kF16 && opt_.multi_precision != 0; }
+
+  int device_, rank_, world_;
+  cudaStream_t stream_ = nullptr;
+  ncclComm* comm_ = nullptr;
+  int key_type_ = -1;  // -1 unknown, 0 int, 1 str
+  std::unordered_map<std::string, int> str_keys_;
+  std::unordered_map<int, KeyInfo> keys_;
+  std::vector<int> unsealed_;
+  std::vector<std::unique_ptr<Segment>> segs_;
+  std::map<std::string, std::unique_ptr<DensePlan>> plans_;
+  std::unordered_map<int, std::shared_ptr<RspKey>> rsp_;
+  b200kv_optimizer opt_;
+  OptScalars sc_;
+  TableRing ring_;
+  DevBuf gnorm_;           // float[2]: scale, norm of the last clipped push
+  bool gnorm_valid_ = false;
+  int64_t launches_ = 0;
+};
+
+}  // namespace b200kv

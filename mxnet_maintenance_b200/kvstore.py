@@ -1,0 +1,473 @@
+"""The B200 kvstore: a drop-in for ``mx.kv.create('device' / 'nccl')`` and
+``gluon.Trainer(kvstore=...)`` registered through ``KVStoreBase.register``
+(python/mxnet/kvstore/base.py:219-243), so ``mx.kv.create('b200')`` finds it.
+
+Method names, argument meaning and error behaviour follow the native wrapper
+python/mxnet/kvstore/kvstore.py:54-736 (``init/push/pull/pushpull/broadcast/row_sparse_pull/
+set_optimizer/save_optimizer_states/load_optimizer_states/type/rank/num_workers``).  Every data
+operation is one call into libb200kv.so with the arrays handed over zero-copy through DLPack;
+nothing is computed in Python and there is no CPU fallback.
+
+One store instance drives one GPU.  Several processes (one per GPU, e.g. under torchrun) cooperate
+through NCCL: gradients are reduce-scattered, each rank updates its shard of the weights and the
+optimizer state, and the new weights are all-gathered (``update_on_kvstore`` semantics preserved:
+after ``pushpull`` every ``out`` holds the updated weight).
+"""
+import ctypes as C
+import os
+import pickle
+
+from . import _lib
+from ._lib import B200KVError, OptimizerDesc, check_call
+from .base import KVStoreBase
+from .dlpack import HandleCache
+from . import optimizer as opt_mod
+
+try:
+    import torch
+except Exception:  # pragma: no cover
+    torch = None
+
+__all__ = ["B200", "RowSparse", "B200KVError"]
+
+
+class RowSparse(object):
+    """Minimal row-sparse array for hosts without MXNet: ``indices`` (int64, sorted unique) and
+    ``data`` ([nnr, ...row shape]) of a ``shape[0]``-row array.  An MXNet ``RowSparseNDArray`` is
+    accepted wherever this class is (same attribute names, python/mxnet/ndarray/sparse.py:276-295)."""
+    stype = "row_sparse"
+
+    def __init__(self, data, indices, shape):
+        self.data, self.indices, self.shape = data, indices, tuple(shape)
+
+
+def _is_rsp(x):
+    return getattr(x, "stype", "default") == "row_sparse"
+
+
+def _is_array(x):
+    return _is_rsp(x) or (torch is not None and isinstance(x, torch.Tensor)) or \
+        hasattr(x, "to_dlpack_for_read") or hasattr(x, "__dlpack__")
+
+
+def _numel(x):
+    return int(x.numel()) if hasattr(x, "numel") else int(x.size)
+
+
+def _flatten(keys, vals):
+    """_ctype_key_value (python/mxnet/kvstore/base.py:32-64): a list under a scalar key means
+    'device copies of that key'.  Returns (keys, arrays, use_str_keys)."""
+    if isinstance(keys, (tuple, list)):
+        assert len(keys) == len(vals)
+        ks, vs, use_str = [], [], None
+        for k, v in zip(keys, vals):
+            k1, v1, s1 = _flatten(k, v)
+            ks += k1
+            vs += v1
+            use_str = s1 if use_str is None else use_str
+            assert use_str == s1, "inconsistent types of keys detected."
+        return ks, vs, use_str
+    assert isinstance(keys, (int, str)), "unexpected type for keys: " + str(type(keys))
+    use_str = isinstance(keys, str)
+    if _is_array(vals):
+        return [keys], [vals], use_str
+    for v in vals:
+        assert _is_array(v)
+    return [keys] * len(vals), list(vals), use_str
+
+
+@KVStoreBase.register
+class B200(KVStoreBase):
+    """``mx.kv.create('b200')``.
+
+    Extensions over the reference API (all optional):
+      * ``clip_global_norm`` attribute: when set, every push clips the merged gradients of that call
+        by their global norm (gluon.utils.clip_global_norm semantics) before the update, so the
+        LAMB + clipping recipe can run sharded on the store;
+      * ``pushpull`` / ``push`` / ``pull`` accept the whole model in one call (lists of keys), which
+        is what makes a step a handful of launches.
+    """
+
+    def __init__(self, device_id=None, rank=None, world_size=None):
+        self._lib = _lib.load()
+        dist = torch is not None and torch.distributed.is_available() and torch.distributed.is_initialized()
+        if rank is None:
+            rank = torch.distributed.get_rank() if dist else 0
+        if world_size is None:
+            world_size = torch.distributed.get_world_size() if dist else 1
+        if device_id is None:
+            device_id = int(os.environ.get("LOCAL_RANK", "0")) if world_size > 1 else (
+                torch.cuda.current_device() if torch is not None and torch.cuda.is_available() else 0)
+        self._device, self._rank, self._world = device_id, rank, world_size
+        h = C.c_void_p()
+        check_call(self._lib.b200kv_create(device_id, rank, world_size, C.byref(h)))
+        self._h = h
+        self._cache = HandleCache()
+        self._updater = None
+        self._opt_sent = None
+        self._str_keys = None
+        self._rsp_shapes = {}
+        self._dense_keys = []
+        self._sizes = {}
+        self.clip_global_norm = None
+        self._bind_stream()
+        if world_size > 1:
+            self._init_comm()
+
+    # ------------------------------------------------------------------ plumbing
+    def __del__(self):
+        h, self._h = getattr(self, "_h", None), None
+        if h:
+            try:
+                self._lib.b200kv_free(h)
+            except Exception:
+                pass
+
+    def _bind_stream(self):
+        """Run on the host framework's current stream so ordering with its kernels is implicit."""
+        if torch is not None and torch.cuda.is_available():
+            s = torch.cuda.current_stream(self._device).cuda_stream
+            check_call(self._lib.b200kv_set_stream(self._h, C.c_void_p(s)))
+
+    def _init_comm(self):
+        """KVStoreNCCL::InitNCCL (kvstore_nccl.h:475-493), one process per GPU: rank 0 creates the
+        NCCL id and ships it through the already-initialised torch.distributed group."""
+        buf = C.create_string_buffer(128)
+        if self._rank == 0:
+            check_call(self._lib.b200kv_comm_unique_id(buf))
+        obj = [buf.raw]
+        torch.distributed.broadcast_object_list(obj, src=0)
+        check_call(self._lib.b200kv_comm_init(self._h, C.create_string_buffer(obj[0], 128)))
+
+    def _keys(self, keys, use_str, create=False):
+        """int keys for the C ABI; string keys are mapped by the store (LookupKeys)."""
+        if self._str_keys is None:
+            self._str_keys = use_str
+        if self._str_keys != use_str:
+            raise B200KVError("inconsistent key types: mixing int and string keys is not allowed")
+        n = len(keys)
+        if not use_str:
+            return (C.c_int * n)(*keys)
+        out = (C.c_int * n)()
+        names = (C.c_char_p * n)(*[k.encode() for k in keys])
+        check_call(self._lib.b200kv_lookup_keys(self._h, n, names, int(create), out))
+        return out
+
+    def _handles(self, arrays, for_write):
+        n = len(arrays)
+        ptrs = (C.c_void_p * n)()
+        keep = [None] * n
+        get = self._cache.get
+        for i, a in enumerate(arrays):
+            ptrs[i], keep[i] = get(a, for_write)
+        return ptrs, keep
+
+    # ------------------------------------------------------------------ optimizer
+    def _send_optimizer(self):
+        o = self._updater.optimizer if self._updater is not None else None
+        if o is None:
+            desc = (0,) * 3 + (0.0,) * 6 + (-1.0, -1.0, -1.0)
+        else:
+            kind = opt_mod.kind_of(o)
+            clip = o.clip_gradient if o.clip_gradient else -1.0     # `if self.clip_gradient:` in the reference
+            gclip = self.clip_global_norm if self.clip_global_norm is not None else -1.0
+            if kind == "sgd":
+                desc = (_lib.OPT_SGD, int(bool(o.multi_precision)), 0,
+                        o.momentum if o.momentum > 0 else 0.0, 0.0, 0.0, 0.0, o.rescale_grad, clip,
+                        -1.0, -1.0, gclip)
+            elif kind == "adam":
+                desc = (_lib.OPT_ADAM, int(bool(o.multi_precision)), 0, 0.0, o.beta1, o.beta2,
+                        o.epsilon, o.rescale_grad, clip, -1.0, -1.0, gclip)
+            else:
+                desc = (_lib.OPT_LAMB, int(bool(o.multi_precision)), int(bool(o.bias_correction)), 0.0,
+                        o.beta1, o.beta2, o.epsilon, o.rescale_grad, clip,
+                        o.lower_bound if o.lower_bound else -1.0,
+                        o.upper_bound if o.upper_bound else -1.0, gclip)
+        if desc != self._opt_sent:
+            d = OptimizerDesc(*desc)
+            check_call(self._lib.b200kv_set_optimizer(self._h, C.byref(d)))
+            self._opt_sent = desc
+
+    def _before_update(self, ckeys, keys):
+        """Ship this step's scalars: the Python side of the updater callback (kvstore.py:34-41,
+        optimizer.py:2078-2127) without any tensor work."""
+        self._send_optimizer()
+        if self._updater is None:
+            return
+        uniq = list(dict.fromkeys(keys))
+        lrs, wds, steps = opt_mod.resolve_step(self._updater.optimizer, uniq)
+        n = len(uniq)
+        ck = self._keys(uniq, isinstance(uniq[0], str)) if uniq else (C.c_int * 0)()
+        check_call(self._lib.b200kv_set_hyper(self._h, n, ck, (C.c_float * n)(*lrs),
+                                              (C.c_float * n)(*wds), (C.c_int * n)(*steps)))
+
+    # ------------------------------------------------------------------ KVStore API
+    def init(self, key, value):
+        """kvstore.py:120-176.  Row-sparse values initialise a row-sparse key."""
+        keys, vals, use_str = _flatten(key, value)
+        ck = self._keys(keys, use_str, create=True)
+        self._bind_stream()
+        dense_idx = [i for i, v in enumerate(vals) if not _is_rsp(v)]
+        for i, v in enumerate(vals):
+            if _is_rsp(v):
+                self._init_rsp(ck[i], v)
+        if dense_idx:
+            dk = (C.c_int * len(dense_idx))(*[ck[i] for i in dense_idx])
+            ptrs, keep = self._handles([vals[i] for i in dense_idx], False)
+            check_call(self._lib.b200kv_init(self._h, len(dense_idx), dk, ptrs))
+            for i in dense_idx:
+                self._dense_keys.append(keys[i])
+                self._sizes[keys[i]] = _numel(vals[i])
+
+    def push(self, key, value, priority=0):
+        """kvstore.py:178-270."""
+        keys, vals, use_str = _flatten(key, value)
+        if vals and _is_rsp(vals[0]):
+            return self._push_rsp(keys, vals, use_str, priority)
+        ck = self._keys(keys, use_str)
+        self._bind_stream()
+        self._before_update(ck, keys)
+        ptrs, keep = self._handles(vals, False)
+        check_call(self._lib.b200kv_push(self._h, len(keys), ck, ptrs, priority))
+
+    def pull(self, key, out=None, priority=0, ignore_sparse=True):
+        """kvstore.py:272-336.  Row-sparse outs are skipped when ignore_sparse (kvstore_local.h:374-385)."""
+        assert out is not None
+        keys, outs, use_str = _flatten(key, out)
+        if ignore_sparse:
+            sel = [i for i, o in enumerate(outs) if not _is_rsp(o)]
+            keys, outs = [keys[i] for i in sel], [outs[i] for i in sel]
+            if not keys:
+                return
+        elif any(_is_rsp(o) for o in outs):
+            raise B200KVError("pull with row_sparse outputs is not supported; use row_sparse_pull")
+        ck = self._keys(keys, use_str)
+        self._bind_stream()
+        ptrs, keep = self._handles(outs, True)
+        check_call(self._lib.b200kv_pull(self._h, len(keys), ck, ptrs, priority))
+
+    def pushpull(self, key, value, out=None, priority=0):
+        """kvstore.py:338-415: push then pull; with out=None the result lands in `value`."""
+        vkeys, vals, use_str = _flatten(key, value)
+        if out is None:
+            okeys, outs = vkeys, vals
+        else:
+            okeys, outs, use_str_o = _flatten(key, out)
+            assert use_str == use_str_o
+        cv = self._keys(vkeys, use_str)
+        co = cv if okeys is vkeys else self._keys(okeys, use_str)
+        self._bind_stream()
+        self._before_update(cv, vkeys)
+        pv, keep_v = self._handles(vals, False)
+        po, keep_o = (pv, keep_v) if outs is vals else self._handles(outs, True)
+        check_call(self._lib.b200kv_pushpull(self._h, len(vkeys), cv, pv, len(okeys), co, po, priority))
+
+    def broadcast(self, key, value, out, priority=0):
+        """kvstore.py:98-118 / base.py:77-95: init with rank 0's value, then pull into `out`."""
+        vkeys, vals, use_str = _flatten(key, value)
+        okeys, outs, _ = _flatten(key, out)
+        cv = self._keys(vkeys, use_str, create=True)
+        co = self._keys(okeys, use_str)
+        self._bind_stream()
+        pv, keep_v = self._handles(vals, False)
+        po, keep_o = self._handles(outs, True)
+        check_call(self._lib.b200kv_broadcast(self._h, len(vkeys), cv, pv, len(okeys), co, po, priority))
+        for k, v in zip(vkeys, vals):
+            self._dense_keys.append(k)
+            self._sizes[k] = _numel(v)
+
+    # ------------------------------------------------------------------ row sparse
+    def _init_rsp(self, ckey, v):
+        raise B200KVError("row-sparse init needs a dense [num_rows, row_len] table: use init_row_sparse")
+
+    def init_row_sparse(self, key, table):
+        """Initialise a row-sparse key from the dense [num_rows, row_len] table holding all rows
+        (what `w.tostype('row_sparse')` of a freshly initialised embedding is; trainer.py:155-157)."""
+        ck = self._keys([key], isinstance(key, str), create=True)
+        self._bind_stream()
+        ptrs, keep = self._handles([table], False)
+        check_call(self._lib.b200kv_init_rsp(self._h, ck[0], ptrs[0]))
+        self._rsp_shapes[key] = tuple(table.shape)
+
+    def _push_rsp(self, keys, vals, use_str, priority):
+        ck = self._keys(keys, use_str)
+        self._bind_stream()
+        groups = {}
+        for k, c, v in zip(keys, ck, vals):
+            groups.setdefault(k, (c, []))[1].append(v)
+        for k, (c, vs) in groups.items():
+            self._send_optimizer()
+            if self._updater is not None:
+                lrs, wds, steps = opt_mod.resolve_step(self._updater.optimizer, [k])
+                check_call(self._lib.b200kv_set_hyper(self._h, 1, (C.c_int * 1)(c), (C.c_float * 1)(*lrs),
+                                                      (C.c_float * 1)(*wds), (C.c_int * 1)(*steps)))
+            pi, keep_i = self._handles([v.indices for v in vs], False)
+            pd, keep_d = self._handles([v.data for v in vs], False)
+            check_call(self._lib.b200kv_push_rsp(self._h, c, len(vs), pi, pd, priority))
+
+    def rsp_merged(self, key):
+        """The merged (reduced) row-sparse gradient of the last push on `key` as a RowSparse."""
+        ck = self._keys([key], isinstance(key, str))
+        n = C.c_int64()
+        check_call(self._lib.b200kv_rsp_merged_size(self._h, ck[0], C.byref(n)))
+        shape = self._rsp_shapes[key]
+        dev = torch.device("cuda", self._device)
+        idx = torch.empty(n.value, dtype=torch.int64, device=dev)
+        val = torch.empty((n.value,) + tuple(shape[1:]), dtype=torch.float32, device=dev)
+        pi, k1 = self._handles([idx], True)
+        pd, k2 = self._handles([val], True)
+        check_call(self._lib.b200kv_rsp_merged_copy(self._h, ck[0], pi[0], pd[0]))
+        return RowSparse(val, idx, shape)
+
+    def row_sparse_pull(self, key, out=None, priority=0, row_ids=None):
+        """kvstore.py:417-495: pulls the rows named by `row_ids` (any shape, unsorted, duplicates
+        allowed) into row-sparse `out`.  A single row_ids with a list of outs pulls once and copies."""
+        assert out is not None and row_ids is not None
+        if _is_array(row_ids) and not isinstance(row_ids, (list, tuple)):
+            row_ids = [row_ids]
+        single = _is_rsp(out)
+        outs = [out] if single else list(out)
+        first_out = outs[:1] if len(row_ids) == 1 and len(outs) > 1 else outs
+        if isinstance(key, (list, tuple)):
+            keys = list(key)
+        else:
+            keys = [key] * len(first_out)
+        assert len(keys) == len(first_out) == len(row_ids), \
+            "the number of row_ids doesn't match the number of values"
+        ck = self._keys(keys, isinstance(keys[0], str))
+        self._bind_stream()
+        dev = torch.device("cuda", self._device)
+        for k, c, o, ids in zip(keys, ck, first_out, row_ids):
+            if not _is_rsp(o):
+                raise B200KVError("row_sparse_pull requires row_sparse outputs")
+            shape = self._rsp_shapes[k]
+            n = int(ids.numel()) if hasattr(ids, "numel") else int(ids.size)
+            idx = torch.empty(max(n, 1), dtype=torch.int64, device=dev)
+            val = torch.empty((max(n, 1),) + tuple(shape[1:]), dtype=torch.float32, device=dev)
+            pr, k0 = self._handles([ids], False)
+            pi, k1 = self._handles([idx], True)
+            pd, k2 = self._handles([val], True)
+            nnr = C.c_int64()
+            check_call(self._lib.b200kv_row_sparse_pull(self._h, c, pr[0], pi[0], pd[0], C.byref(nnr),
+                                                        priority))
+            o.indices, o.data, o.shape = idx[:nnr.value], val[:nnr.value], shape
+        if first_out is not outs:
+            for o in outs[1:]:
+                o.indices, o.data, o.shape = outs[0].indices.clone(), outs[0].data.clone(), outs[0].shape
+
+    # ------------------------------------------------------------------ optimizer / capabilities
+    def set_optimizer(self, optimizer):
+        """kvstore.py:553-600.  SGD, Adam and LAMB run on the store; anything else raises so that
+        the Trainer falls back to update_on_kvstore=False."""
+        opt_mod.kind_of(optimizer)
+        self._updater = opt_mod.Updater(optimizer)
+        self._send_optimizer()
+
+    def _set_updater(self, updater):
+        raise NotImplementedError("custom Python updaters are not supported: the b200 store runs "
+                                  "its own fused CUDA updates (set_optimizer) or none")
+
+    def set_gradient_compression(self, compression_params):
+        """2-bit compression is lossy and useless on NVLink; refused like KVStoreNCCL does
+        (src/kvstore/kvstore_nccl.h:183-186)."""
+        raise B200KVError("gradient compression is not supported by the b200 kvstore")
+
+    def is_capable(self, capability):
+        if capability.lower() == KVStoreBase.OPTIMIZER:
+            return True
+        raise ValueError("Unknown capability: {}".format(capability))
+
+    @property
+    def type(self):
+        return "b200"
+
+    @property
+    def rank(self):
+        return self._rank
+
+    @property
+    def num_workers(self):
+        return self._world
+
+    def _barrier(self):
+        check_call(self._lib.b200kv_barrier(self._h))
+
+    def wait(self):
+        """Block until every enqueued operation has finished (NDArray.wait_to_read on the outs)."""
+        check_call(self._lib.b200kv_wait(self._h))
+
+    def launch_count(self):
+        n = C.c_int64()
+        check_call(self._lib.b200kv_launch_count(self._h, C.byref(n)))
+        return n.value
+
+    def last_global_norm(self):
+        v = C.c_float()
+        check_call(self._lib.b200kv_last_global_norm(self._h, C.byref(v)))
+        return v.value
+
+    # ------------------------------------------------------------------ checkpointing
+    def _collect_states(self):
+        """Gather the (possibly sharded) optimizer state back into the reference's per-index layout
+        (optimizer.py:252-255,583-600,1264-1268,1602-1607): SGD `mom` | `(mom, w32)`;
+        Adam/LAMB `(mean, var)` | `(w32, (mean, var))`.  Collective when num_workers > 1."""
+        assert self._updater is not None
+        kind = opt_mod.kind_of(self._updater.optimizer)
+        states = {}
+        dev = torch.device("cuda", self._device)
+        for key in dict.fromkeys(self._dense_keys):
+            ck = self._keys([key], isinstance(key, str))
+            got = []
+            for which in (0, 1, 2):
+                n = self._key_size(key)
+                buf = torch.empty(n, dtype=torch.float32, device=dev)
+                p, keep = self._handles([buf], True)
+                present = C.c_int()
+                check_call(self._lib.b200kv_get_state(self._h, ck[0], which, p[0], C.byref(present)))
+                got.append(buf.cpu().numpy() if present.value else None)
+            s0, s1, w32 = got
+            if s0 is None and s1 is None and w32 is None and kind != "sgd":
+                continue
+            if kind == "sgd":
+                st = s0 if w32 is None else (s0, w32)
+            else:
+                st = (s0, s1) if w32 is None else (w32, (s0, s1))
+            states[key] = st
+        self.wait()
+        self._updater.states = states
+        return states
+
+    def _key_size(self, key):
+        return self._sizes[key]
+
+    def save_optimizer_states(self, fname, dump_optimizer=False):
+        """kvstore.py:641-666."""
+        assert self._updater is not None, "Cannot save states for distributed training"
+        self._collect_states()
+        with open(fname, 'wb') as fout:
+            fout.write(self._updater.get_states(dump_optimizer))
+
+    def load_optimizer_states(self, fname):
+        """kvstore.py:668-690."""
+        assert self._updater is not None, "Cannot load states for distributed training"
+        with open(fname, 'rb') as f:
+            self._updater.set_states(f.read())
+        self._opt_sent = None
+        self._send_optimizer()
+        kind = opt_mod.kind_of(self._updater.optimizer)
+        dev = torch.device("cuda", self._device)
+        for key, st in self._updater.states.items():
+            if kind == "sgd":
+                s0, s1, w32 = (st[0], None, st[1]) if isinstance(st, tuple) else (st, None, None)
+            elif isinstance(st[1], tuple):
+                w32, (s0, s1) = st
+            else:
+                (s0, s1), w32 = st, None
+            ck = self._keys([key], isinstance(key, str))
+            for which, arr in ((2, w32), (0, s0), (1, s1)):
+                if arr is None:
+                    continue
+                t = torch.as_tensor(arr, dtype=torch.float32).reshape(-1).to(dev)
+                p, keep = self._handles([t], False)
+                check_call(self._lib.b200kv_set_state(self._h, ck[0], which, p[0]))
+        self.wait()

@@ -1,0 +1,108 @@
+"""Store-less fused multi-tensor optimizer ops — the B200 forms of the NNVM ops a local
+``Updater`` calls when ``update_on_kvstore=False``:
+
+  multi_sgd_update / multi_sgd_mom_update / multi_mp_sgd_update / multi_mp_sgd_mom_update
+      (src/operator/optimizer_op-inl.h:207-380; python wrappers python/mxnet/ndarray/contrib.py)
+  adam_update over a tensor list (optimizer_op-inl.h:1252-1340), fused mixed precision
+  multi_lamb_update / multi_mp_lamb_update (src/operator/contrib/multi_lamb-inl.h:51-340)
+  multi_sum_sq (src/operator/contrib/multi_sum_sq-inl.h:88-103)
+
+Arguments are lists of CUDA torch tensors updated in place (MXNet NDArrays can be passed through
+``torch.from_dlpack``-style zero-copy views by the adapter).  All arithmetic happens in
+libb200kv.so on the current CUDA stream.
+"""
+import ctypes as C
+
+import torch
+
+from . import _lib
+from ._lib import check_call
+
+
+def _pp(tensors):
+    n = len(tensors)
+    a = (C.c_void_p * n)()
+    for i, t in enumerate(tensors):
+        a[i] = t.data_ptr()
+    return a
+
+
+def _dtype_flag(t):
+    if t.dtype == torch.float32:
+        return 0
+    if t.dtype == torch.float16:
+        return 2
+    raise TypeError("only float32 / float16 tensors are supported, got %s" % t.dtype)
+
+
+def _common(weights, grads):
+    assert len(weights) == len(grads) and len(weights) > 0
+    for w, g in zip(weights, grads):
+        assert w.is_cuda and g.is_cuda and w.is_contiguous() and g.is_contiguous()
+        assert w.dtype == g.dtype and w.numel() == g.numel()
+    n = len(weights)
+    sizes = (C.c_int64 * n)(*[w.numel() for w in weights])
+    stream = C.c_void_p(torch.cuda.current_stream(weights[0].device).cuda_stream)
+    return n, sizes, stream
+
+
+def _f(vals, n):
+    if not isinstance(vals, (list, tuple)):
+        vals = [vals] * n
+    return (C.c_float * n)(*vals)
+
+
+def multi_sgd_update(weights, grads, lrs, wds, moms=None, weights32=None, momentum=0.0,
+                     rescale_grad=1.0, clip_gradient=-1.0):
+    """moms=None: multi_(mp_)sgd_update; else multi_(mp_)sgd_mom_update.  weights32 selects mp."""
+    lib = _lib.load()
+    n, sizes, stream = _common(weights, grads)
+    with torch.cuda.device(weights[0].device):
+        check_call(lib.b200kv_multi_sgd_update(
+            n, _dtype_flag(weights[0]), _pp(weights), _pp(grads),
+            _pp(moms) if moms is not None else None,
+            _pp(weights32) if weights32 is not None else None, sizes, _f(lrs, n), _f(wds, n),
+            momentum, rescale_grad, clip_gradient if clip_gradient is not None else -1.0, stream))
+
+
+def multi_adam_update(weights, grads, means, vars_, lrs, wds, weights32=None, beta1=0.9, beta2=0.999,
+                      epsilon=1e-8, rescale_grad=1.0, clip_gradient=-1.0):
+    lib = _lib.load()
+    n, sizes, stream = _common(weights, grads)
+    with torch.cuda.device(weights[0].device):
+        check_call(lib.b200kv_multi_adam_update(
+            n, _dtype_flag(weights[0]), _pp(weights), _pp(grads), _pp(means), _pp(vars_),
+            _pp(weights32) if weights32 is not None else None, sizes, _f(lrs, n), _f(wds, n), beta1,
+            beta2, epsilon, rescale_grad, clip_gradient if clip_gradient is not None else -1.0, stream))
+
+
+def multi_lamb_update(weights, grads, means, vars_, lrs, wds, step_count, weights32=None, beta1=0.9,
+                      beta2=0.999, epsilon=1e-6, rescale_grad=1.0, clip_gradient=-1.0,
+                      lower_bound=-1.0, upper_bound=-1.0, bias_correction=True):
+    lib = _lib.load()
+    n, sizes, stream = _common(weights, grads)
+    if not isinstance(step_count, (list, tuple)):
+        step_count = [step_count] * n
+    with torch.cuda.device(weights[0].device):
+        check_call(lib.b200kv_multi_lamb_update(
+            n, _dtype_flag(weights[0]), _pp(weights), _pp(grads), _pp(means), _pp(vars_),
+            _pp(weights32) if weights32 is not None else None, sizes, _f(lrs, n), _f(wds, n),
+            (C.c_int * n)(*step_count), beta1, beta2, epsilon, rescale_grad,
+            clip_gradient if clip_gradient is not None else -1.0,
+            lower_bound if lower_bound is not None else -1.0,
+            upper_bound if upper_bound is not None else -1.0, int(bool(bias_correction)), stream))
+
+
+def multi_sum_sq(arrays):
+    """Returns a float32 CUDA tensor with sum(x*x) per array."""
+    lib = _lib.load()
+    n = len(arrays)
+    for a in arrays:
+        assert a.is_cuda and a.is_contiguous()
+    out = torch.empty(n, dtype=torch.float32, device=arrays[0].device)
+    sizes = (C.c_int64 * n)(*[a.numel() for a in arrays])
+    stream = C.c_void_p(torch.cuda.current_stream(arrays[0].device).cuda_stream)
+    with torch.cuda.device(arrays[0].device):
+        check_call(lib.b200kv_multi_sum_sq(n, _dtype_flag(arrays[0]), _pp(arrays), sizes,
+                                           C.c_void_p(out.data_ptr()), stream))
+    return out

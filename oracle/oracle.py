@@ -122,10 +122,11 @@ class Oracle:
         has_mom = moms is not None
         has_mp = w32s is not None
         sizes = _i64([w.size for w in weights])
+        lrs, wds = _f32(lrs), _f32(wds)   # keep the arrays alive across the call
         rc = self.lib.mxref_multi_sgd(_flag(weights[0]), int(has_mom), int(has_mp), len(weights),
                                       _pp(weights), _pp(grads), _pp(moms) if has_mom else None,
                                       _pp(w32s) if has_mp else None, _pp(outs), sizes.ctypes.data,
-                                      _f32(lrs).ctypes.data, _f32(wds).ctypes.data, momentum, rescale,
+                                      lrs.ctypes.data, wds.ctypes.data, momentum, rescale,
                                       clip, self.nthread)
         assert rc == 0
 
@@ -158,10 +159,11 @@ class Oracle:
         r1 = np.zeros(n, np.float32)
         r2 = np.zeros(n, np.float32)
         st = np.ascontiguousarray(np.asarray(steps, dtype=np.int32))
+        lrs, wds = _f32(lrs), _f32(wds)   # keep the arrays alive across the call
         rc = self.lib.mxref_multi_lamb(_flag(weights[0]), int(has_mp), n, _pp(weights), _pp(grads),
                                        _pp(means), _pp(vars_), _pp(w32s) if has_mp else None,
-                                       _pp(weights), sizes.ctypes.data, _f32(lrs).ctypes.data,
-                                       _f32(wds).ctypes.data, st.ctypes.data, beta1, beta2, eps,
+                                       _pp(weights), sizes.ctypes.data, lrs.ctypes.data,
+                                       wds.ctypes.data, st.ctypes.data, beta1, beta2, eps,
                                        rescale, clip, lower, upper, int(bias_correction),
                                        self.nthread, r1.ctypes.data, r2.ctypes.data)
         assert rc == 0

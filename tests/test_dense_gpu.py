@@ -1,0 +1,179 @@
+"""Parity of the CUDA path with the CPU oracle for the dense gradient-sync + update path, through
+the kvstore plugin API (which calls the C ABI).  fp32 paths are compared BIT-EXACTLY wherever the
+reduction order is the reference's (device-local copies are summed in CommCPU order); LAMB norms
+use a tree reduction instead of the CPU's sequential sum, so LAMB is compared at the north-star
+tolerance rtol 1e-5 / atol 1e-6 (fp32) and rtol 2e-3 (fp16 weights)."""
+import numpy as np
+import pytest
+
+torch = pytest.importorskip("torch")
+pytestmark = pytest.mark.gpu
+
+RTOL32, ATOL32 = 1e-5, 1e-6     # BASELINE.json north_star: fp32 weights / states per step
+RTOL16 = 2e-3                   # fp16-gradient / fp32-master paths
+
+
+def _mb():
+    import mxnet_maintenance_b200 as mb
+    return mb
+
+
+def _shapes(name):
+    from mxnet_maintenance_b200 import shapes
+    if name == "ragged":   # edge cases: 1 element, non-multiples of 4, chunk boundaries +-1
+        return [(1,), (3,), (5, 1), (4095,), (4096,), (4097,), (2, 4099), (8192,), (33, 7, 3), (100003,)]
+    return shapes.CONFIGS[name]()
+
+
+def _run(oracle, shape_name, opt_kind, ncopies, steps=3, mp=False, clip=None, gclip=None, batch=True,
+         momentum=0.9, seed=0, wd=1e-4):
+    from oracle.oracle import LocalStoreModel
+    mb = _mb()
+    rng = np.random.default_rng(1234 + seed)
+    shp = _shapes(shape_name)
+    wdt = np.float16 if mp else np.float32
+    w0 = [rng.uniform(-1, 1, s).astype(np.float32).astype(wdt) for s in shp]
+    keys = list(range(len(shp)))
+    # LAMB runs at its C4 learning rate; the others at a deliberately large one
+    lr = 1e-3 if opt_kind == "lamb" else 0.05
+    common = dict(learning_rate=lr, wd=wd, rescale_grad=1.0 / 8, clip_gradient=clip, multi_precision=mp)
+    odict = dict(lr=lr, wd=wd, rescale=1.0 / 8, clip=clip if clip else -1.0, multi_precision=mp)
+    if opt_kind == "sgd":
+        opt = mb.optimizer.SGD(momentum=momentum, **common)
+        odict.update(kind="sgd", momentum=momentum)
+    elif opt_kind == "adam":
+        opt = mb.optimizer.Adam(**common)
+        odict.update(kind="adam")
+    elif opt_kind == "lamb":
+        opt = mb.optimizer.LAMB(**common)
+        odict.update(kind="lamb")
+    else:
+        opt = None
+        odict = None
+    kv = mb.create("b200")
+    if opt is not None:
+        kv.set_optimizer(opt)
+    if gclip is not None:
+        kv.clip_global_norm = gclip
+    model = LocalStoreModel(oracle, odict)
+    dev_w = [torch.from_numpy(w).cuda() for w in w0]
+    for k, w in zip(keys, w0):
+        model.init(k, w)
+    kv.broadcast(keys, dev_w, [[w] for w in dev_w])
+    results = []
+    for step in range(steps):
+        grads = [[(rng.uniform(-1, 1, s) * 1e-2).astype(np.float32).astype(wdt) for _ in range(ncopies)]
+                 for s in shp]
+        dev_g = [[torch.from_numpy(g).cuda() for g in gs] for gs in grads]
+        if batch:
+            kv.pushpull(keys, dev_g, out=[[w] for w in dev_w])
+        else:
+            for k in keys:
+                kv.pushpull(k, dev_g[k], out=dev_w[k])
+        kv.wait()
+        if gclip is not None:
+            merged = [oracle.reduce_sum([g.copy() for g in gs]).astype(np.float32) for gs in grads]
+            oracle.clip_global_norm(merged, gclip)
+            ref = [model.pushpull(k, [merged[k].astype(wdt)]) for k in keys]
+        else:
+            ref = [model.pushpull(k, grads[k]) for k in keys]
+        got = [w.cpu().numpy() for w in dev_w]
+        results.append((got, ref))
+    return kv, model, results
+
+
+def _assert_bits(results):
+    for step, (got, ref) in enumerate(results):
+        for k, (a, b) in enumerate(zip(got, ref)):
+            assert a.tobytes() == b.tobytes(), "key %d step %d: max |diff| %g" % (
+                k, step, np.abs(a.astype(np.float64) - b.astype(np.float64)).max())
+
+
+def _assert_close(results, rtol, atol):
+    for step, (got, ref) in enumerate(results):
+        for k, (a, b) in enumerate(zip(got, ref)):
+            np.testing.assert_allclose(a.astype(np.float32), b.astype(np.float32), rtol=rtol, atol=atol,
+                                       err_msg="key %d step %d" % (k, step))
+
+
+@pytest.mark.parametrize("ncopies", [1, 2, 4, 5, 8])
+def test_sgd_mom_ragged_bit_exact(oracle, ncopies):
+    _, _, res = _run(oracle, "ragged", "sgd", ncopies)
+    _assert_bits(res)
+
+
+@pytest.mark.parametrize("clip", [None, 0.0005])
+@pytest.mark.parametrize("momentum", [0.9, 0.0])
+def test_sgd_variants_bit_exact(oracle, clip, momentum):
+    _, _, res = _run(oracle, "ragged", "sgd", 3, clip=clip, momentum=momentum)
+    _assert_bits(res)
+
+
+def test_sgd_mom_mlp_4copies_bit_exact(oracle):
+    """C1: Gluon MLP, 4 device copies, SGD momentum 0.9 (the reference's CPU-runnable config)."""
+    _, _, res = _run(oracle, "mlp", "sgd", 4)
+    _assert_bits(res)
+
+
+def test_sgd_mom_resnet50_bit_exact(oracle):
+    """C2 at one GPU: all 161 arrays in one pushpull."""
+    kv, _, res = _run(oracle, "resnet50", "sgd", 1)
+    _assert_bits(res)
+    # broadcast unpack + 3 fused update launches, nothing per key
+    assert kv.launch_count() <= 8
+
+
+def test_per_key_calls_match_batched(oracle):
+    _, _, res = _run(oracle, "mlp", "sgd", 2, batch=False)
+    _assert_bits(res)
+
+
+def test_mp_sgd_mom_bit_exact(oracle):
+    """multi_mp_sgd_mom_update: fp16 grads/weights, fp32 master + momentum (C3 kernel)."""
+    _, _, res = _run(oracle, "ragged", "sgd", 1, mp=True)
+    _assert_bits(res)
+    _, _, res = _run(oracle, "ragged", "sgd", 4, mp=True)   # fp16 CommCPU sum: rounds after each add
+    _assert_bits(res)
+
+
+@pytest.mark.parametrize("clip", [None, 0.0005])
+def test_adam_bit_exact(oracle, clip):
+    _, _, res = _run(oracle, "ragged", "adam", 2, clip=clip, wd=0.01)
+    _assert_bits(res)
+
+
+def test_mp_adam_bit_exact(oracle):
+    """fused fp16-grad -> fp32 Adam -> fp16 weight equals the reference's cast/update/cast wrapper."""
+    _, _, res = _run(oracle, "ragged", "adam", 1, mp=True, wd=0.01)
+    _assert_bits(res)
+
+
+def test_lamb_close(oracle):
+    _, _, res = _run(oracle, "ragged", "lamb", 1, wd=0.01)
+    _assert_close(res, RTOL32, ATOL32)
+    _, _, res = _run(oracle, "ragged", "lamb", 4, wd=0.01, clip=0.001)
+    _assert_close(res, RTOL32, ATOL32)
+
+
+def test_mp_lamb_close(oracle):
+    _, _, res = _run(oracle, "ragged", "lamb", 1, mp=True, wd=0.01)
+    _assert_close(res, RTOL16, 1e-3)
+
+
+def test_lamb_global_norm_clip_close(oracle):
+    """C4 recipe: allreduce -> clip_global_norm -> multi_lamb_update, run on the store."""
+    kv, _, res = _run(oracle, "ragged", "lamb", 2, wd=0.01, gclip=0.05)
+    _assert_close(res, RTOL32, ATOL32)
+    assert kv.last_global_norm() > 0.05
+
+
+def test_no_optimizer_assigns_merged(oracle):
+    """push without an updater replaces the stored value by the merged one (kvstore_local.h:268-274)."""
+    _, _, res = _run(oracle, "ragged", None, 4)
+    _assert_bits(res)
+
+
+def test_bert_base_mp_sgd_one_step(oracle):
+    """C3 shapes (109M parameters), one step, bit-exact."""
+    _, _, res = _run(oracle, "bert_base", "sgd", 1, mp=True, steps=1)
+    _assert_bits(res)

@@ -103,6 +103,16 @@ int b200kv_pull(b200kv_handle h, int num, const int* keys, DLManagedTensor* cons
  * (kvstore_local.h:336-343). */
 int b200kv_pushpull(b200kv_handle h, int vnum, const int* vkeys, DLManagedTensor* const* vals,
                     int onum, const int* okeys, DLManagedTensor* const* outs, int priority);
+/* A pushpull whose argument list is validated, grouped and planned ONCE and then replayed every
+ * step with b200kv_run_bound — the arrays (MXNet's persistent gradient / weight buffers) must stay
+ * alive and in place until b200kv_unbind.  Equivalent to calling b200kv_pushpull with the same
+ * arguments each step; it removes the per-call handle marshalling that the reference pays per key
+ * (src/c_api/c_api.cc:2707-2731 copies every NDArray handle on every call). */
+int b200kv_bind_pushpull(b200kv_handle h, int vnum, const int* vkeys, DLManagedTensor* const* vals,
+                         int onum, const int* okeys, DLManagedTensor* const* outs, int* out_id);
+int b200kv_run_bound(b200kv_handle h, int id);
+int b200kv_unbind(b200kv_handle h, int id);
+
 /* MXKVStoreBroadcast (c_api.h:2880): init + pull (kvstore_local.h:327-334). */
 int b200kv_broadcast(b200kv_handle h, int vnum, const int* vkeys, DLManagedTensor* const* vals,
                      int onum, const int* okeys, DLManagedTensor* const* outs, int priority);
@@ -166,6 +176,12 @@ int b200kv_get_type(b200kv_handle h, const char** out);
 int b200kv_get_rank(b200kv_handle h, int* out);
 int b200kv_get_group_size(b200kv_handle h, int* out);
 int b200kv_barrier(b200kv_handle h);
+/* CUDA-event timing of the optimizer-update kernels on the store's stream (the analogue of the
+ * reference's engine-op profiler hooks, src/engine/threaded_engine.h:354-362): while enabled every
+ * update section is bracketed by two events; profile_read synchronises, returns the summed
+ * milliseconds and the number of sections, and resets. */
+int b200kv_set_profiling(b200kv_handle h, int enable);
+int b200kv_profile_read(b200kv_handle h, double* kernel_ms, int64_t* count);
 /* number of kernels this store has launched so far (bench.py's gpu_launches) */
 int b200kv_launch_count(b200kv_handle h, int64_t* out);
 

@@ -46,6 +46,11 @@ SIGNATURES = {
     "b200kv_pull": [_VP, _I, _PI, _PVP, _I],
     "b200kv_pushpull": [_VP, _I, _PI, _PVP, _I, _PI, _PVP, _I],
     "b200kv_broadcast": [_VP, _I, _PI, _PVP, _I, _PI, _PVP, _I],
+    "b200kv_bind_pushpull": [_VP, _I, _PI, _PVP, _I, _PI, _PVP, _PI],
+    "b200kv_run_bound": [_VP, _I],
+    "b200kv_unbind": [_VP, _I],
+    "b200kv_set_profiling": [_VP, _I],
+    "b200kv_profile_read": [_VP, C.POINTER(C.c_double), C.POINTER(_I64)],
     "b200kv_set_optimizer": [_VP, C.POINTER(OptimizerDesc)],
     "b200kv_set_hyper": [_VP, _I, _PI, _PF, _PF, _PI],
     "b200kv_last_global_norm": [_VP, _PF],

@@ -111,6 +111,37 @@ int b200kv_pushpull(b200kv_handle h, int vnum, const int* vkeys, DLManagedTensor
   API_END();
 }
 
+int b200kv_bind_pushpull(b200kv_handle h, int vnum, const int* vkeys, DLManagedTensor* const* vals,
+                         int onum, const int* okeys, DLManagedTensor* const* outs, int* out_id) {
+  API_BEGIN();
+  *out_id = S(h)->bind(Store::kPushPull, vnum, vkeys, vals, onum, okeys, outs);
+  API_END();
+}
+
+int b200kv_run_bound(b200kv_handle h, int id) {
+  API_BEGIN();
+  S(h)->run_bound(id);
+  API_END();
+}
+
+int b200kv_unbind(b200kv_handle h, int id) {
+  API_BEGIN();
+  S(h)->unbind(id);
+  API_END();
+}
+
+int b200kv_set_profiling(b200kv_handle h, int enable) {
+  API_BEGIN();
+  S(h)->set_profiling(enable != 0);
+  API_END();
+}
+
+int b200kv_profile_read(b200kv_handle h, double* kernel_ms, int64_t* count) {
+  API_BEGIN();
+  S(h)->profile_read(kernel_ms, count);
+  API_END();
+}
+
 int b200kv_broadcast(b200kv_handle h, int vnum, const int* vkeys, DLManagedTensor* const* vals,
                      int onum, const int* okeys, DLManagedTensor* const* outs, int) {
   API_BEGIN();

@@ -408,8 +408,10 @@ void Store::run_class(Mode mode, DensePlan& p, const std::vector<const Entry*>& 
       MtaCall c = base;
       c.blob = dev + o_upd; c.ngrad = ng; c.nout = no; c.plan = &p.full;
       if (has_opt()) {
+        prof_begin();
         const float* gscale = opt_.clip_global_norm >= 0.f ? global_norm_scale(p, p.full, c) : nullptr;
         update_chunks(p, p.full, c, gscale);
+        prof_end();
         if (mp) s.w_stale = true;
       } else {
         // no updater: the merged value replaces the stored one (kvstore_local.h:268-274)
@@ -480,8 +482,10 @@ void Store::run_class(Mode mode, DensePlan& p, const std::vector<const Entry*>& 
       }
       MtaCall u = base;
       u.blob = dev + o_upd; u.ngrad = upd_ng; u.nout = upd_no; u.plan = &p.shard;
+      prof_begin();
       const float* gscale = opt_.clip_global_norm >= 0.f ? global_norm_scale(p, p.shard, u) : nullptr;
       update_chunks(p, p.shard, u, gscale);
+      prof_end();
       if (p.full_segment) {
         NCCL_OK(nccl->AllGather(at(s.wbuf, rank_ * s.slice, es), s.wbuf.p, s.slice, nt_type, comm, stream_));
       } else {
@@ -521,11 +525,10 @@ void Store::pull_staged(const Entry& e) {
     if (bytes) CUDA_OK(cudaMemcpyAsync(o.data, ki.staged->p, bytes, cudaMemcpyDeviceToDevice, stream_));
 }
 
-void Store::dense(Mode mode, int vnum, const int* vkeys, DLManagedTensor* const* vals, int onum,
-                  const int* okeys, DLManagedTensor* const* outs) {
-  use_device();
+void Store::prepare(Mode mode, int vnum, const int* vkeys, DLManagedTensor* const* vals, int onum,
+                    const int* okeys, DLManagedTensor* const* outs, BoundCall* bc, bool allow_staged) {
   // GroupKVPairs (kvstore_local.h:417-447): entries with the same key are device copies of it
-  std::vector<Entry> ents;
+  std::vector<Entry>& ents = bc->ents;
   std::unordered_map<int, size_t> where;
   auto entry = [&](int key) -> Entry& {
     auto it = where.find(key);
@@ -536,22 +539,21 @@ void Store::dense(Mode mode, int vnum, const int* vkeys, DLManagedTensor* const*
     return ents[it->second];
   };
   auto check = [&](const TensorView& v, int key, const char* what) {
+    KV_CHECK(rsp_.find(key) == rsp_.end(), what << ": key " << key
+                                                << " is row_sparse; use the row-sparse entry points");
     const KeyInfo& ki = info(key);
-    KV_CHECK(!ki.rsp, what << ": key " << key << " is row_sparse; use the row-sparse entry points");
     KV_CHECK(v.dtype == ki.dtype, what << ": dtype mismatch for key " << key);
     KV_CHECK(v.numel == ki.size, what << ": key " << key << " holds " << ki.size << " elements, got "
                                       << v.numel);
   };
   if (mode & kPush)
     for (int i = 0; i < vnum; ++i) {
-      KV_CHECK(rsp_.find(vkeys[i]) == rsp_.end(), "key " << vkeys[i] << " is row_sparse; use b200kv_push_rsp");
       const TensorView v = view_of(vals[i], device_, "push value");
       check(v, vkeys[i], "push");
       entry(vkeys[i]).vals.push_back(v);
     }
   if (mode & kPull)
     for (int i = 0; i < onum; ++i) {
-      KV_CHECK(rsp_.find(okeys[i]) == rsp_.end(), "key " << okeys[i] << " is row_sparse; use b200kv_row_sparse_pull");
       const TensorView v = view_of(outs[i], device_, "pull out");
       check(v, okeys[i], "pull");
       entry(okeys[i]).outs.push_back(v);
@@ -562,11 +564,11 @@ void Store::dense(Mode mode, int vnum, const int* vkeys, DLManagedTensor* const*
   if (need_seal) seal();
 
   // classes: (pushes?, segment, #vals, #outs) -> entries sorted by flat offset
-  struct Cls { int mode, seg, ng, no; std::vector<const Entry*> ents; };
-  std::vector<Cls> classes;
+  std::vector<Cls>& classes = bc->classes;
   for (const Entry& e : ents) {
     const KeyInfo& ki = keys_[e.key];
     if (ki.seg < 0) {  // only pulled, never pushed yet: serve from the staged init value
+      KV_CHECK(allow_staged, "cannot bind a pull of key " << e.key << " before its first push");
       pull_staged(e);
       continue;
     }
@@ -577,24 +579,89 @@ void Store::dense(Mode mode, int vnum, const int* vkeys, DLManagedTensor* const*
     for (auto& x : classes)
       if (x.mode == m && x.seg == ki.seg && x.ng == ng && x.no == no) c = &x;
     if (!c) {
-      classes.push_back(Cls{m, ki.seg, ng, no, {}});
+      classes.push_back(Cls{m, ki.seg, ng, no, {}, nullptr});
       c = &classes.back();
     }
     c->ents.push_back(&e);
   }
   // pushes first, then pure pulls (PushPullImpl = PushImpl; PullImpl, kvstore_local.h:336-343)
-  for (int pass = 0; pass < 2; ++pass)
-    for (auto& c : classes) {
-      if ((pass == 0) != ((c.mode & kPush) != 0)) continue;
-      std::sort(c.ents.begin(), c.ents.end(), [&](const Entry* a, const Entry* b) {
-        return keys_[a->key].off < keys_[b->key].off;
-      });
-      std::vector<int> ks;
-      ks.reserve(c.ents.size());
-      for (const Entry* e : c.ents) ks.push_back(e->key);
-      DensePlan& p = plan_for(c.seg, ks, c.ng, c.no);
-      run_class(static_cast<Mode>(c.mode), p, c.ents);
-    }
+  std::stable_sort(classes.begin(), classes.end(), [](const Cls& a, const Cls& b) {
+    return ((a.mode & kPush) != 0) > ((b.mode & kPush) != 0);
+  });
+  for (auto& c : classes) {
+    std::sort(c.ents.begin(), c.ents.end(), [&](const Entry* a, const Entry* b) {
+      return keys_[a->key].off < keys_[b->key].off;
+    });
+    std::vector<int> ks;
+    ks.reserve(c.ents.size());
+    for (const Entry* e : c.ents) ks.push_back(e->key);
+    c.plan = &plan_for(c.seg, ks, c.ng, c.no);
+  }
+}
+
+void Store::execute(BoundCall& bc) {
+  for (auto& c : bc.classes) run_class(static_cast<Mode>(c.mode), *c.plan, c.ents);
+}
+
+void Store::dense(Mode mode, int vnum, const int* vkeys, DLManagedTensor* const* vals, int onum,
+                  const int* okeys, DLManagedTensor* const* outs) {
+  use_device();
+  BoundCall bc;
+  bc.ents.reserve(static_cast<size_t>(vnum + onum));
+  prepare(mode, vnum, vkeys, vals, onum, okeys, outs, &bc, true);
+  execute(bc);
+}
+
+int Store::bind(Mode mode, int vnum, const int* vkeys, DLManagedTensor* const* vals, int onum,
+                const int* okeys, DLManagedTensor* const* outs) {
+  use_device();
+  std::unique_ptr<BoundCall> bc(new BoundCall());
+  bc->ents.reserve(static_cast<size_t>(vnum + onum));   // Entry addresses must stay put
+  prepare(mode, vnum, vkeys, vals, onum, okeys, outs, bc.get(), false);
+  const int id = next_bound_++;
+  bound_.emplace(id, std::move(bc));
+  return id;
+}
+
+void Store::run_bound(int id) {
+  use_device();
+  auto it = bound_.find(id);
+  KV_CHECK(it != bound_.end(), "unknown bound call " << id);
+  execute(*it->second);
+}
+
+void Store::unbind(int id) { bound_.erase(id); }
+
+// ---- kernel timing ---------------------------------------------------------------------------------
+void Store::prof_begin() {
+  if (!profiling_) return;
+  if (prof_used_ == prof_events_.size()) {
+    cudaEvent_t a, b;
+    CUDA_OK(cudaEventCreate(&a));
+    CUDA_OK(cudaEventCreate(&b));
+    prof_events_.emplace_back(a, b);
+  }
+  CUDA_OK(cudaEventRecord(prof_events_[prof_used_].first, stream_));
+}
+
+void Store::prof_end() {
+  if (!profiling_) return;
+  CUDA_OK(cudaEventRecord(prof_events_[prof_used_].second, stream_));
+  ++prof_used_;
+}
+
+void Store::profile_read(double* ms, int64_t* count) {
+  use_device();
+  CUDA_OK(cudaStreamSynchronize(stream_));
+  double total = 0;
+  for (size_t i = 0; i < prof_used_; ++i) {
+    float t = 0;
+    CUDA_OK(cudaEventElapsedTime(&t, prof_events_[i].first, prof_events_[i].second));
+    total += t;
+  }
+  *ms = total;
+  *count = static_cast<int64_t>(prof_used_);
+  prof_used_ = 0;
 }
 
 // ---- optimizer state access (checkpointing) --------------------------------------------------------

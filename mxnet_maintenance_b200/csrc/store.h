@@ -71,6 +71,14 @@ class Store {
   enum Mode { kPush = 1, kPull = 2, kPushPull = 3 };
   void dense(Mode mode, int vnum, const int* vkeys, DLManagedTensor* const* vals, int onum,
              const int* okeys, DLManagedTensor* const* outs);
+  // a pushpull whose arguments were validated, grouped and planned once (same arrays every step)
+  int bind(Mode mode, int vnum, const int* vkeys, DLManagedTensor* const* vals, int onum,
+           const int* okeys, DLManagedTensor* const* outs);
+  void run_bound(int id);
+  void unbind(int id);
+  // CUDA-event timing of the update kernels (bench.py's roofline leg)
+  void set_profiling(bool on) { profiling_ = on; }
+  void profile_read(double* ms, int64_t* count);
   void set_optimizer(const b200kv_optimizer& opt);
   void set_hyper(int num, const int* keys, const float* lrs, const float* wds, const int* steps);
   float last_global_norm();
@@ -97,6 +105,20 @@ class Store {
     int key;
     std::vector<TensorView> vals, outs;
   };
+  struct Cls {
+    int mode, seg, ng, no;
+    std::vector<const Entry*> ents;
+    DensePlan* plan = nullptr;
+  };
+  struct BoundCall {
+    std::vector<Entry> ents;
+    std::vector<Cls> classes;
+  };
+  void prepare(Mode mode, int vnum, const int* vkeys, DLManagedTensor* const* vals, int onum,
+               const int* okeys, DLManagedTensor* const* outs, BoundCall* bc, bool allow_staged);
+  void execute(BoundCall& bc);
+  void prof_begin();
+  void prof_end();
   KeyInfo& info(int key);
   void use_device();
   void check_key_type(bool is_str);
@@ -127,6 +149,11 @@ class Store {
   DevBuf gnorm_;           // float[2]: scale, norm of the last clipped push
   bool gnorm_valid_ = false;
   int64_t launches_ = 0;
+  std::unordered_map<int, std::unique_ptr<BoundCall>> bound_;
+  int next_bound_ = 1;
+  bool profiling_ = false;
+  std::vector<std::pair<cudaEvent_t, cudaEvent_t>> prof_events_;
+  size_t prof_used_ = 0;
 };
 
 }  // namespace b200kv

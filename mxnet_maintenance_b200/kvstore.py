@@ -76,6 +76,80 @@ def _flatten(keys, vals):
     return [keys] * len(vals), list(vals), use_str
 
 
+class BoundStep(object):
+    """A replayable pushpull (see B200.bind_pushpull).  Each call ships this step's scalars and runs
+    the pre-planned launch sequence.  The scalar refresh is the vectorised, value-identical form of
+    ``resolve_step``: counters advance by one, the scheduler is evaluated once, and per-key
+    multipliers are re-read only when they changed."""
+
+    def __init__(self, kv, bid, keys, keep):
+        self.kv, self.bid, self.keys, self._keep = kv, bid, keys, keep
+        self.n = len(keys)
+        self._ck = kv._keys(keys, isinstance(keys[0], str))
+        self._first = True          # bind itself resolved the scalars of the first replay
+        self._sig = None
+        self._lr_mult = self._wd_mult = None
+        self._steps = (C.c_int * self.n)()
+
+    def _mult_signature(self, o):
+        pd = o.param_dict
+        return (tuple([(pd[k].lr_mult, pd[k].wd_mult) for k in self.keys if k in pd]) if pd else (),
+                tuple(o.lr_mult.items()), tuple(o.wd_mult.items()), len(o.idx2name))
+
+    def _refresh(self):
+        kv = self.kv
+        kv._send_optimizer()
+        up = kv._updater
+        if up is None:
+            return
+        o = up.optimizer
+        import numpy as np
+        sig = self._mult_signature(o)
+        if sig != self._sig:
+            # multipliers exactly as _get_lrs/_get_wds apply them (optimizer.py:437-494), probed
+            # with unit lr / wd so that lr * mult reproduces the reference's double product
+            lr0, wd0, sch = o.lr, o.wd, o.lr_scheduler
+            try:
+                o.lr, o.wd, o.lr_scheduler = 1.0, 1.0, None
+                self._lr_mult = np.asarray(o._get_lrs(self.keys), dtype=np.float64)
+                self._wd_mult = np.asarray(o._get_wds(self.keys), dtype=np.float64)
+            finally:
+                o.lr, o.wd, o.lr_scheduler = lr0, wd0, sch
+            self._sig = sig
+        if hasattr(o, "_set_current_context"):
+            o._set_current_context(0)
+        o._update_count(self.keys)
+        cnt = o._index_update_count
+        steps = [cnt[k] for k in self.keys]
+        lr = o.lr_scheduler(o.num_update) if o.lr_scheduler is not None else o.lr
+        lrs = lr * self._lr_mult
+        wds = o.wd * self._wd_mult
+        if opt_mod.kind_of(o) == "adam":
+            import math
+            coef = {}
+            for t in set(steps):
+                coef[t] = math.sqrt(1. - o.beta2 ** t) / (1. - o.beta1 ** t)
+            lrs = lrs * np.asarray([coef[t] for t in steps], dtype=np.float64)
+        lrs32 = np.ascontiguousarray(lrs, dtype=np.float32)
+        wds32 = np.ascontiguousarray(wds, dtype=np.float32)
+        self._steps[:] = steps
+        check_call(kv._lib.b200kv_set_hyper(
+            kv._h, self.n, self._ck, lrs32.ctypes.data_as(C.POINTER(C.c_float)),
+            wds32.ctypes.data_as(C.POINTER(C.c_float)), self._steps))
+
+    def __call__(self):
+        if self._first:
+            self._first = False
+        else:
+            self._refresh()
+        check_call(self.kv._lib.b200kv_run_bound(self.kv._h, self.bid))
+
+    def release(self):
+        if self.bid:
+            check_call(self.kv._lib.b200kv_unbind(self.kv._h, self.bid))
+            self.bid = 0
+
+
 @KVStoreBase.register
 class B200(KVStoreBase):
     """``mx.kv.create('b200')``.
@@ -261,6 +335,36 @@ class B200(KVStoreBase):
         pv, keep_v = self._handles(vals, False)
         po, keep_o = (pv, keep_v) if outs is vals else self._handles(outs, True)
         check_call(self._lib.b200kv_pushpull(self._h, len(vkeys), cv, pv, len(okeys), co, po, priority))
+
+    def bind_pushpull(self, key, value, out=None):
+        """Returns a callable that replays ``pushpull(key, value, out)`` on the SAME arrays every
+        step (MXNet's gradient and weight buffers are persistent, python/mxnet/gluon/parameter.py
+        ``_init_grad``): handles are exported, validated and planned once, so a step costs one
+        scalar refresh plus one C call instead of marshalling hundreds of handles."""
+        vkeys, vals, use_str = _flatten(key, value)
+        if out is None:
+            okeys, outs = vkeys, vals
+        else:
+            okeys, outs, _ = _flatten(key, out)
+        cv = self._keys(vkeys, use_str)
+        co = cv if okeys is vkeys else self._keys(okeys, use_str)
+        self._bind_stream()
+        self._before_update(cv, vkeys)   # the first replay is a normal step
+        pv, keep_v = self._handles(vals, False)
+        po, keep_o = (pv, keep_v) if outs is vals else self._handles(outs, True)
+        bid = C.c_int()
+        check_call(self._lib.b200kv_bind_pushpull(self._h, len(vkeys), cv, pv, len(okeys), co, po,
+                                                  C.byref(bid)))
+        return BoundStep(self, bid.value, list(dict.fromkeys(vkeys)), (vals, outs, keep_v, keep_o))
+
+    def set_profiling(self, enable):
+        check_call(self._lib.b200kv_set_profiling(self._h, int(bool(enable))))
+
+    def profile_read(self):
+        """(milliseconds spent in update kernels, number of update sections) since the last read."""
+        ms, n = C.c_double(), C.c_int64()
+        check_call(self._lib.b200kv_profile_read(self._h, C.byref(ms), C.byref(n)))
+        return ms.value, n.value
 
     def broadcast(self, key, value, out, priority=0):
         """kvstore.py:98-118 / base.py:77-95: init with rank 0's value, then pull into `out`."""

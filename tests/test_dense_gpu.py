@@ -177,3 +177,52 @@ def test_bert_base_mp_sgd_one_step(oracle):
     """C3 shapes (109M parameters), one step, bit-exact."""
     _, _, res = _run(oracle, "bert_base", "sgd", 1, mp=True, steps=1)
     _assert_bits(res)
+
+
+@pytest.mark.parametrize("kind", ["sgd", "adam", "lamb"])
+def test_bound_step_equals_pushpull(kind):
+    """bind_pushpull replays must be bit-identical with plain pushpull calls on the same inputs,
+    including the per-step scalars (lr schedule, lr/wd multipliers, update counts)."""
+    import mxnet_maintenance_b200 as mb
+
+    class Sched:
+        base_lr = 0.02
+
+        def __call__(self, n):
+            return self.base_lr / (1 + n)
+
+    class P:
+        def __init__(self, lm, wm):
+            self.lr_mult, self.wd_mult = lm, wm
+
+    shp = _shapes("ragged")
+    keys = list(range(len(shp)))
+    rng = np.random.default_rng(7)
+    w0 = [rng.uniform(-1, 1, s).astype(np.float32) for s in shp]
+    g = [[(rng.uniform(-1, 1, s) * 1e-2).astype(np.float32) for s in shp] for _ in range(4)]
+    res = []
+    for bound in (False, True):
+        O = {"sgd": mb.optimizer.SGD, "adam": mb.optimizer.Adam, "lamb": mb.optimizer.LAMB}[kind]
+        kw = dict(momentum=0.9) if kind == "sgd" else {}
+        opt = O(learning_rate=0.02, lr_scheduler=Sched(), wd=1e-3,
+                param_dict={k: P(1.0 + 0.25 * (k % 3), 0.5 * (k % 2)) for k in keys}, **kw)
+        kv = mb.create("b200")
+        kv.set_optimizer(opt)
+        w = [torch.from_numpy(x).cuda() for x in w0]
+        gd = [torch.empty_like(x) for x in w]
+        kv.broadcast(keys, w, [[x] for x in w])
+        step = kv.bind_pushpull(keys, gd, out=[[x] for x in w]) if bound else None
+        for it in range(4):
+            for d, h in zip(gd, g[it]):
+                d.copy_(torch.from_numpy(h))
+            if it == 2:
+                opt.param_dict[1].lr_mult = 3.0     # multipliers may change mid-training
+            if bound:
+                step()
+            else:
+                kv.pushpull(keys, gd, out=[[x] for x in w])
+        kv.wait()
+        res.append([x.cpu().numpy() for x in w])
+        assert opt.num_update == 4 and opt._index_update_count[0] == 4
+    for a, b in zip(*res):
+        assert a.tobytes() == b.tobytes()

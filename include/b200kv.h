@@ -219,6 +219,27 @@ int b200kv_multi_lamb_update(int num, int dtype, void* const* weights, const voi
 int b200kv_multi_sum_sq(int num, int dtype, const void* const* arrays, const int64_t* sizes,
                         float* out, void* stream);
 
+/* b200kv_multi_sum_sq_static — no counterpart in the reference.
+ * Same result as b200kv_multi_sum_sq (bit for bit), for callers that cannot allocate device memory
+ * while they run: a framework whose own pool has already taken the GPU's memory (a late cudaMalloc
+ * from a plugin may fail there), a trainer that cannot tolerate the device-wide synchronisation
+ * cudaMalloc implies, or a process that must know a library's footprint up front.  This entry
+ * point never allocates (no cudaMalloc / cudaFree / cudaMallocHost, no framework allocator): its
+ * tensor table, chunk list and per-chunk partial sums live in one fixed array inside the library
+ * image — every GPU that loads libb200kv.so holds those 343,296 bytes until the process exits.
+ * Limits (a clear error is returned beyond them): at most B200KV_STATIC_MAX_ARRAYS arrays and
+ * B200KV_STATIC_MAX_CHUNKS chunks of 4096 elements (sum over arrays of ceil(size/4096)) per call.
+ * The first call on each device looks up where that GPU placed the array; make that first call
+ * before starting any stream capture.  All calls share the one array and it keeps whatever the
+ * previous call wrote (nothing in it needs clearing between calls); two calls whose GPU work
+ * overlaps — different streams, or different threads — would overwrite each other's tables, so
+ * order them on one stream or with events.  `arrays`/`sizes` are host arrays; `out` is a device
+ * pointer to `num` floats. */
+#define B200KV_STATIC_MAX_ARRAYS 256
+#define B200KV_STATIC_MAX_CHUNKS 16384
+int b200kv_multi_sum_sq_static(int num, int dtype, const void* const* arrays, const int64_t* sizes,
+                               float* out, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -386,7 +386,7 @@ mta_kernel(const MtaArgs a, const Op op, const float* __restrict__ gscale,
 // second stage of the deterministic reduction: one warp per tensor sums that tensor's chunk
 // partials (chunks of a tensor are consecutive: [first[t], first[t+1])).  sums is [nred][nt];
 // accumulate != 0 adds to the existing value (used when a tensor list is processed in pieces).
-__global__ void reduce_partials_kernel(const float* __restrict__ partials,
+static __global__ void reduce_partials_kernel(const float* __restrict__ partials,
                                        const int* __restrict__ first, int nt, int nred,
                                        float* __restrict__ sums) {
   const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
@@ -403,7 +403,7 @@ __global__ void reduce_partials_kernel(const float* __restrict__ partials,
 }
 
 // LAMB trust ratio per tensor (multi_lamb.cc:92-104): sums = [sum w^2 | sum u^2], each [nt]
-__global__ void lamb_ratio_kernel(const float* __restrict__ sums, int nt, float lower, float upper,
+static __global__ void lamb_ratio_kernel(const float* __restrict__ sums, int nt, float lower, float upper,
                                   float* __restrict__ ratio) {
   const int t = blockIdx.x * blockDim.x + threadIdx.x;
   if (t >= nt) return;
@@ -416,7 +416,7 @@ __global__ void lamb_ratio_kernel(const float* __restrict__ sums, int nt, float 
 
 // clip_global_norm scalar (gluon/utils.py:149-154): out[0] = scale = min(max_norm/(norm+1e-8), 1),
 // out[1] = norm.  One block; per-tensor sums are added in a fixed tree order.
-__global__ void global_norm_kernel(const float* __restrict__ sums, int nt, float max_norm,
+static __global__ void global_norm_kernel(const float* __restrict__ sums, int nt, float max_norm,
                                    float* __restrict__ out) {
   __shared__ float s[kThreads];
   float x = 0.f;

@@ -106,3 +106,26 @@ def multi_sum_sq(arrays):
         check_call(lib.b200kv_multi_sum_sq(n, _dtype_flag(arrays[0]), _pp(arrays), sizes,
                                            C.c_void_p(out.data_ptr()), stream))
     return out
+
+
+STATIC_MAX_ARRAYS, STATIC_MAX_CHUNKS = 256, 16384
+
+
+def multi_sum_sq_static(arrays, out=None):
+    """multi_sum_sq for callers that must not allocate GPU memory while they run (a framework pool
+    owns the device memory, or a cudaMalloc-induced device synchronisation is unacceptable): the
+    library works inside a fixed ~335 KiB array that is part of its image.  At most 256 arrays and
+    16384 chunks of 4096 elements per call; pass `out` (float32, len(arrays)) to avoid even the
+    result allocation.  Calls share that one array, so keep them ordered on one stream."""
+    lib = _lib.load()
+    n = len(arrays)
+    for a in arrays:
+        assert a.is_cuda and a.is_contiguous()
+    if out is None:
+        out = torch.empty(n, dtype=torch.float32, device=arrays[0].device)
+    sizes = (C.c_int64 * n)(*[a.numel() for a in arrays])
+    stream = C.c_void_p(torch.cuda.current_stream(arrays[0].device).cuda_stream)
+    with torch.cuda.device(arrays[0].device):
+        check_call(lib.b200kv_multi_sum_sq_static(n, _dtype_flag(arrays[0]), _pp(arrays), sizes,
+                                                  C.c_void_p(out.data_ptr()), stream))
+    return out

@@ -1,0 +1,135 @@
+"""Pins the plain-C oracle (oracle/oracle.c) to the reference's OWN functors compiled in place from
+/root/reference (oracle/_ref): bit-for-bit equality on randomized inputs.  Skipped where the
+reference tree / oracle/_ref is absent (the GPU box); the committed golden vectors cover that."""
+import numpy as np
+import pytest
+
+
+def _both(port, ref, fn):
+    return fn(port), fn(ref)
+
+
+@pytest.mark.parametrize("dt", [np.float32, np.float16])
+@pytest.mark.parametrize("n", [1, 2, 3, 4, 5, 8, 9])
+def test_commcpu_reduce(oracle, oracle_ref, dt, n):
+    rng = np.random.default_rng(n)
+    for size in (1000, 1_200_000):   # below / above MXNET_KVSTORE_BIGARRAY_BOUND (threaded split)
+        base = [(rng.uniform(-1, 1, size) * 1e-2).astype(dt) for _ in range(n)]
+        a, b = _both(oracle, oracle_ref, lambda o: o.reduce_sum([x.copy() for x in base]))
+        assert a.tobytes() == b.tobytes()
+
+
+@pytest.mark.parametrize("clip", [-1.0, 0.005])
+@pytest.mark.parametrize("mom", [0.0, 0.9])
+@pytest.mark.parametrize("mp", [False, True])
+def test_multi_sgd(oracle, oracle_ref, clip, mom, mp):
+    rng = np.random.default_rng(1)
+    sizes = [7, 1000, 4097, 70000]
+    dt = np.float16 if mp else np.float32
+    w = [rng.uniform(-1, 1, s).astype(np.float32).astype(dt) for s in sizes]
+    g = [(rng.uniform(-1, 1, s) * 1e-2).astype(np.float32).astype(dt) for s in sizes]
+    m = [rng.uniform(-1, 1, s).astype(np.float32) * 1e-2 for s in sizes]
+
+    def f(o):
+        ww = [x.copy() for x in w]
+        mm = [x.copy() for x in m]
+        w32 = [x.astype(np.float32) for x in w] if mp else None
+        for _ in range(2):
+            o.multi_sgd(ww, g, mm if mom else None, w32, [0.1, 0.2, 0.05, 0.3], [1e-4, 0, 1e-3, 1e-2], mom,
+                        0.5, clip)
+        return np.concatenate([x.astype(np.float32) for x in ww] + mm + (w32 or []))
+    a, b = _both(oracle, oracle_ref, f)
+    assert a.tobytes() == b.tobytes()
+    # and the closed form for one element, so that a shared wiring mistake cannot hide
+    w1, g1 = np.array([0.5], np.float32), np.array([0.01], np.float32)
+    oracle.multi_sgd([w1], [g1], None, None, [0.1], [0.0], 0.0, 1.0, -1.0)
+    assert w1[0] == np.float32(0.5) + (np.float32(0) - np.float32(0.1) * np.float32(0) * np.float32(0.5)
+                                       - np.float32(0.1) * np.float32(1.0) * np.float32(0.01))
+
+
+def test_single_tensor_sgd_mom(oracle, oracle_ref):
+    rng = np.random.default_rng(2)
+    w = rng.uniform(-1, 1, 5000).astype(np.float32)
+    g = (rng.uniform(-1, 1, 5000) * 1e-2).astype(np.float32)
+
+    def f(o):
+        ww, mm = w.copy(), np.zeros_like(w)
+        o.sgd_mom(ww, g, mm, 0.1, 1e-3, 0.9, 0.5, -1.0)
+        o.sgd_mom(ww, g, mm, 0.1, 1e-3, 0.9, 0.5, 0.002)
+        w16, g16 = w.astype(np.float16), g.astype(np.float16)
+        w32, m2 = w16.astype(np.float32), np.zeros_like(w)
+        o.mp_sgd_mom(w16, g16, m2, w32, 0.1, 1e-3, 0.9, 0.5, -1.0)
+        return np.concatenate([ww, mm, w16.astype(np.float32), w32, m2])
+    a, b = _both(oracle, oracle_ref, f)
+    assert a.tobytes() == b.tobytes()
+
+
+@pytest.mark.parametrize("clip", [-1.0, 0.005])
+def test_adam(oracle, oracle_ref, clip):
+    rng = np.random.default_rng(3)
+    s = 100003
+    w = rng.uniform(-1, 1, s).astype(np.float32)
+    g = (rng.uniform(-1, 1, s) * 1e-2).astype(np.float32)
+
+    def f(o):
+        ww, mean, var = w.copy(), np.zeros(s, np.float32), np.zeros(s, np.float32)
+        for t in (1, 2, 3):
+            o.adam(ww, g, mean, var, 1e-4 * t, 0.01, 0.9, 0.999, 1e-8, 0.5, clip)
+        return np.concatenate([ww, mean, var])
+    a, b = _both(oracle, oracle_ref, f)
+    assert a.tobytes() == b.tobytes()
+
+
+@pytest.mark.parametrize("mp", [False, True])
+@pytest.mark.parametrize("bc", [True, False])
+def test_multi_lamb(oracle, oracle_ref, mp, bc):
+    rng = np.random.default_rng(4)
+    sizes = [5, 1024, 30000, 100001]
+    dt = np.float16 if mp else np.float32
+    w = [rng.uniform(-1, 1, s).astype(np.float32).astype(dt) for s in sizes]
+    g = [(rng.uniform(-1, 1, s) * 1e-2).astype(np.float32).astype(dt) for s in sizes]
+
+    def f(o):
+        ww = [x.copy() for x in w]
+        me = [np.zeros(s, np.float32) for s in sizes]
+        va = [np.zeros(s, np.float32) for s in sizes]
+        w32 = [x.astype(np.float32) for x in ww] if mp else None
+        outs = []
+        for t in (1, 2, 3):
+            r1, r2 = o.multi_lamb(ww, g, me, va, w32, [1e-3, 2e-3, 1e-3, 5e-4], [0.01, 0.0, 0.02, 0.01],
+                                  [t, t, t + 1, t], rescale=0.5, clip=0.004 if t == 2 else -1.0,
+                                  bias_correction=bc)
+            outs += [r1, r2]
+        return np.concatenate([x.astype(np.float32) for x in ww] + me + va + outs)
+    a, b = _both(oracle, oracle_ref, f)
+    assert a.tobytes() == b.tobytes()
+
+
+def test_multi_sum_sq(oracle, oracle_ref):
+    rng = np.random.default_rng(5)
+    arrs = [rng.uniform(-1, 1, s).astype(np.float32) for s in (3, 1000, 200000)]
+    for dt in (np.float32, np.float16):
+        aa = [x.astype(dt) for x in arrs]
+        a, b = _both(oracle, oracle_ref, lambda o: o.multi_sum_sq(aa))
+        assert a.tobytes() == b.tobytes()
+
+
+def test_row_sparse_kernels(oracle, oracle_ref):
+    rng = np.random.default_rng(6)
+    W = rng.uniform(-1, 1, (50, 8)).astype(np.float32)
+    idx = np.array([1, 5, 7, 30], np.int64)
+    gg = rng.uniform(-1, 1, (4, 8)).astype(np.float32)
+
+    def f(o):
+        ww, mm = W.copy(), np.zeros_like(W)
+        o.sgd_mom_rsp(ww, mm, idx, gg, 0.1, 1e-3, 0.9)
+        o.sgd_mom_rsp(ww, mm, idx, gg, 0.1, 1e-3, 0.9, 0.5, 0.1)
+        me, va = np.zeros_like(W), np.zeros_like(W)
+        o.adam_rsp(ww, me, va, idx, gg, 1e-3, 0.01)
+        o.adam_rsp(ww, me, va, idx, gg, 1e-3, 0.01, clip=0.2)
+        return np.concatenate([ww.ravel(), mm.ravel(), me.ravel(), va.ravel()])
+    a, b = _both(oracle, oracle_ref, f)
+    assert a.tobytes() == b.tobytes()
+    ra = oracle.sparse_retain(idx, gg, [0, 1, 7, 29, 30, 49])
+    rb = oracle_ref.sparse_retain(idx, gg, [0, 1, 7, 29, 30, 49])
+    assert ra[0].tobytes() == rb[0].tobytes() and ra[1].tobytes() == rb[1].tobytes()

@@ -1,0 +1,128 @@
+"""Multi-GPU parity check, one process per GPU:
+
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 \
+        --master-port 29533 tests/multi_gpu_check.py
+
+Every rank pushes its own gradient set; the expected result is the CPU oracle's CommCPU reduce over
+the ranks' gradients followed by the reference optimizer functor.  With two ranks an fp32 / fp16
+sum of two numbers is order-independent, so N=2 must be BIT-EXACT; for N>2 NCCL's reduction order
+differs from CommCPU's and the north-star tolerances apply (fp32 rtol 1e-5 / atol 1e-6 per step,
+fp16-gradient paths rtol 2e-3)."""
+import os
+import sys
+
+import numpy as np
+import torch
+import torch.distributed as dist
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+
+
+def main():
+    rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
+    torch.cuda.set_device(local)
+    dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    import mxnet_maintenance_b200 as mb
+    from oracle.oracle import Oracle, LocalStoreModel
+    oracle = Oracle("port")
+    shp = [(1,), (3,), (4095,), (4097,), (2, 4099), (33, 7, 3), (100003,), (64,), (300, 300)]
+    keys = list(range(len(shp)))
+    failures = []
+
+    def run(kind, mp=False, gclip=None, batch=True, steps=3, ncopies=1):
+        wdt = np.float16 if mp else np.float32
+        rng_w = np.random.default_rng(77)
+        w0 = [rng_w.uniform(-1, 1, s).astype(np.float32).astype(wdt) for s in shp]
+        lr = 1e-3 if kind == "lamb" else 0.05
+        common = dict(learning_rate=lr, wd=0.01, rescale_grad=1.0 / 8, multi_precision=mp)
+        odict = dict(lr=lr, wd=0.01, rescale=1.0 / 8, multi_precision=mp, kind=kind)
+        if kind == "sgd":
+            opt = mb.optimizer.SGD(momentum=0.9, **common); odict["momentum"] = 0.9
+        elif kind == "adam":
+            opt = mb.optimizer.Adam(**common)
+        elif kind == "lamb":
+            opt = mb.optimizer.LAMB(**common)
+        else:
+            opt, odict = None, None
+        kv = mb.create("b200")
+        assert kv.num_workers == world and kv.rank == rank
+        if opt is not None:
+            kv.set_optimizer(opt)
+        if gclip is not None:
+            kv.clip_global_norm = gclip
+        model = LocalStoreModel(oracle, odict)
+        # rank 0's value wins the broadcast: give the other ranks garbage to prove it
+        dev_w = [torch.from_numpy(w if rank == 0 else w * 0 + 7).cuda() for w in w0]
+        for k, w in zip(keys, w0):
+            model.init(k, w)
+        kv.broadcast(keys, dev_w, [[w] for w in dev_w])
+        for step in range(steps):
+            # gradients of every rank (all ranks can compute all of them from the seeds)
+            allg = []
+            for r in range(world):
+                rg = np.random.default_rng(1000 * step + r)
+                allg.append([[(rg.uniform(-1, 1, s) * 1e-2).astype(np.float32).astype(wdt)
+                              for _ in range(ncopies)] for s in shp])
+            mine = [[torch.from_numpy(g).cuda() for g in gs] for gs in allg[rank]]
+            if batch:
+                kv.pushpull(keys, mine, out=[[w] for w in dev_w])
+            else:
+                for k in keys:
+                    kv.pushpull(k, mine[k], out=dev_w[k])
+            kv.wait()
+            # oracle: device-local copies first (CommCPU order), then across ranks (CommCPU order)
+            merged = []
+            for k in keys:
+                per_rank = [oracle.reduce_sum([g.copy() for g in allg[r][k]]) for r in range(world)]
+                merged.append(oracle.reduce_sum([g.copy() for g in per_rank]))
+            if gclip is not None:
+                m32 = [m.astype(np.float32) for m in merged]
+                oracle.clip_global_norm(m32, gclip)
+                merged = [m.astype(wdt) for m in m32]
+            ref = [model.pushpull(k, [merged[k]]) for k in keys]
+            for k in keys:
+                got = dev_w[k].cpu().numpy()
+                exact = world == 2 and kind != "lamb" and gclip is None
+                if exact:
+                    ok = got.tobytes() == ref[k].tobytes()
+                else:
+                    rtol, atol = (2e-3, 1e-3) if mp else (1e-5, 1e-6)
+                    ok = np.allclose(got.astype(np.float32), ref[k].astype(np.float32), rtol=rtol, atol=atol)
+                if not ok:
+                    d = np.abs(got.astype(np.float64) - ref[k].astype(np.float64)).max()
+                    failures.append("%s mp=%s gclip=%s batch=%s step %d key %d maxdiff %g" % (
+                        kind, mp, gclip, batch, step, k, d))
+        return kv, model
+
+    run("sgd")
+    run("sgd", batch=False)            # per-key calls: grouped ncclReduce / ncclBroadcast pieces
+    run("sgd", ncopies=3)
+    run("sgd", mp=True)
+    run("adam")
+    run("adam", mp=True)
+    kv, model = run("lamb")
+    run("lamb", gclip=0.05)
+    run(None)                          # no optimizer: all-reduce, merged value assigned
+    run(None, batch=False)
+
+    # sharded optimizer state gathers back to the full per-key arrays (checkpointing)
+    kv2, model2 = run("sgd", steps=2)
+    st = kv2._collect_states()
+    for k in keys:
+        mom_ref = model2.state[k][0]
+        if not np.array_equal(st[k].reshape(-1), mom_ref) and world == 2:
+            failures.append("state gather key %d" % k)
+
+    t = torch.tensor([len(failures)], device="cuda")
+    dist.all_reduce(t)
+    if rank == 0:
+        for f in failures[:20]:
+            print("FAIL", f)
+        print("MULTI_GPU_CHECK", "FAILED" if t.item() else "OK", "world", world)
+    dist.destroy_process_group()
+    sys.exit(1 if t.item() else 0)
+
+
+if __name__ == "__main__":
+    main()

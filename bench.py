@@ -288,7 +288,8 @@ def run_b200(args):
     t_host = time.perf_counter() - t_host0
     barrier()
     ms = e0.elapsed_time(e1)
-    kernel_ms, kernel_n = kv.profile_read()
+    phases = kv.profile_read_phases()
+    kernel_ms, kernel_n = phases["update"]
     kv.set_profiling(False)
     launches = kv.launch_count() - l0
     if world > 1:
@@ -370,6 +371,7 @@ def run_b200(args):
         roof = {"bound": "nvlink", "achieved": bus, "peak": 900.0, "unit": "GB/s", "frac": bus / 900.0,
                 "traffic": None, "kernel": "ncclReduceScatter + sharded update + ncclAllGather",
                 "step_lower_bound_ms": bound_s * 1e3, "step_frac_of_lower_bound": bound_s * 1e3 / ms_step,
+                "phase_ms_per_step": {k: v[0] / max(v[1], 1) for k, v in phases.items()},
                 "note": "achieved = NCCL bus-bandwidth convention 2*S*(N-1)/N / step time, peak = nominal "
                         "NVLink 5 900 GB/s per direction"}
 

@@ -182,6 +182,10 @@ int b200kv_barrier(b200kv_handle h);
  * milliseconds and the number of sections, and resets. */
 int b200kv_set_profiling(b200kv_handle h, int enable);
 int b200kv_profile_read(b200kv_handle h, double* kernel_ms, int64_t* count);
+/* the same, split by phase: [0] update kernels, [1] pack, [2] reduce(-scatter), [3] all-gather /
+ * broadcast, [4] unpack (the reference names these engine ops "KVStoreReduce", "KVStoreBCast", …,
+ * src/kvstore/comm.h:171,264; kvstore_nccl.h:316,420) */
+int b200kv_profile_read_phases(b200kv_handle h, double ms[8], int64_t count[8]);
 /* number of kernels this store has launched so far (bench.py's gpu_launches) */
 int b200kv_launch_count(b200kv_handle h, int64_t* out);
 

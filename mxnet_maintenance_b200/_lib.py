@@ -51,6 +51,7 @@ SIGNATURES = {
     "b200kv_unbind": [_VP, _I],
     "b200kv_set_profiling": [_VP, _I],
     "b200kv_profile_read": [_VP, C.POINTER(C.c_double), C.POINTER(_I64)],
+    "b200kv_profile_read_phases": [_VP, C.POINTER(C.c_double), C.POINTER(_I64)],
     "b200kv_set_optimizer": [_VP, C.POINTER(OptimizerDesc)],
     "b200kv_set_hyper": [_VP, _I, _PI, _PF, _PF, _PI],
     "b200kv_last_global_norm": [_VP, _PF],

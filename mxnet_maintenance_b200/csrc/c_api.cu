@@ -142,6 +142,12 @@ int b200kv_profile_read(b200kv_handle h, double* kernel_ms, int64_t* count) {
   API_END();
 }
 
+int b200kv_profile_read_phases(b200kv_handle h, double ms[8], int64_t count[8]) {
+  API_BEGIN();
+  S(h)->profile_read_phases(ms, count);
+  API_END();
+}
+
 int b200kv_broadcast(b200kv_handle h, int vnum, const int* vkeys, DLManagedTensor* const* vals,
                      int onum, const int* okeys, DLManagedTensor* const* outs, int) {
   API_BEGIN();

@@ -34,6 +34,14 @@ int launch_copy(const MtaCall& c, bool to_w, bool to_out, bool w_is_f32 = false)
 // out copies (dtype) <- W section (fp32 master)
 int launch_master_to_out(const MtaCall& c);
 
+// peer-memory barrier (see optim.cuh): which = 0 "gradients ready", 1 "weights written"
+struct P2PFlagsHost {
+  uint32_t* flags[kMaxCopies];
+  int world, rank;
+  uint32_t epoch;
+};
+int launch_p2p_barrier(const P2PFlagsHost& f, int which, cudaStream_t stream);
+
 int launch_reduce_partials(const float* partials, const ChunkPlan& plan, int nred, float* sums,
                            cudaStream_t stream);
 int launch_lamb_ratio(const float* sums, int nt, float lower, float upper, float* ratio,

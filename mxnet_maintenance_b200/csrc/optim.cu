@@ -9,9 +9,16 @@ namespace b200kv {
 
 namespace {
 
-int grid_for(const MtaCall& c) {
-  // two resident 256-thread CTAs per SM (launch bounds), sized as a multiple of the SM count
-  const int g = sm_count(c.device) * 2;
+// persistent grid: SM count x resident CTAs per SM for this instantiation (occupancy API, cached)
+template <class K>
+int grid_for(const MtaCall& c, K kernel) {
+  static int per_sm = 0;
+  if (per_sm == 0) {
+    int n = 0;
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, kernel, kThreads, 0) != cudaSuccess || n < 1) n = 2;
+    per_sm = n;
+  }
+  const int g = sm_count(c.device) * per_sm;
   return c.plan->nchunks < g ? (c.plan->nchunks > 0 ? c.plan->nchunks : 1) : g;
 }
 
@@ -32,10 +39,15 @@ int launch_ng(const MtaCall& c, const Op& op, const float* gscale, float* partia
   KV_CHECK(c.ngrad >= 1 && c.ngrad <= kMaxCopies, "unsupported number of gradient copies " << c.ngrad);
   KV_CHECK(c.nout >= 0 && c.nout <= kMaxCopies, "unsupported number of output copies " << c.nout);
   const MtaArgs a = args_of(c);
-  if (c.ngrad == 1)
-    mta_kernel<Op, T, WT, 1><<<grid_for(c), kThreads, 0, c.stream>>>(a, op, gscale, partials);
-  else
-    mta_kernel<Op, T, WT, 0><<<grid_for(c), kThreads, 0, c.stream>>>(a, op, gscale, partials);
+#define GO(NG)                                                                                     \
+  mta_kernel<Op, T, WT, NG><<<grid_for(c, mta_kernel<Op, T, WT, NG>), kThreads, 0, c.stream>>>(a, op, gscale, \
+                                                                                              partials)
+  if (!Op::F.read_g || c.ngrad == 1) GO(1);
+  else if (c.ngrad == 2) GO(2);
+  else if (c.ngrad == 4) GO(4);
+  else if (c.ngrad == 8) GO(8);
+  else GO(0);
+#undef GO
   CUDA_OK(cudaGetLastError());
   return 1;
 }
@@ -101,6 +113,17 @@ int launch_master_to_out(const MtaCall& c) {
   MasterToOutOp op;
   KV_CHECK(c.dtype == kF16, "master_to_out is for fp16 outputs");
   return launch_ng<MasterToOutOp, __half, float>(c, op, nullptr, nullptr);
+}
+
+int launch_p2p_barrier(const P2PFlagsHost& h, int which, cudaStream_t stream) {
+  P2PFlags f;
+  for (int k = 0; k < kMaxCopies; ++k) f.flags[k] = h.flags[k];
+  f.world = h.world;
+  f.rank = h.rank;
+  f.epoch = h.epoch;
+  p2p_barrier_kernel<<<1, 32, 0, stream>>>(f, which);
+  CUDA_OK(cudaGetLastError());
+  return 1;
 }
 
 int launch_reduce_partials(const float* partials, const ChunkPlan& plan, int nred, float* sums,

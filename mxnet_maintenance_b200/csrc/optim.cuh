@@ -79,10 +79,17 @@ __device__ __forceinline__ const uint64_t* sec(const MtaArgs& a, int s) {
 // gradient fetch: NG == 1 is the hot path; NG == 0 means "a.ngrad copies, summed in CommCPU order"
 //   acc = g0;  acc += g1 (+ g2 (+ g3 (+ g4)));  acc += g5 + ...       (comm.h:362-391)
 // ------------------------------------------------------------------------------------------------
+// vectors per thread issued before any use: fewer when many copies are summed, so that all peer
+// loads of a vector are in flight together without blowing the register budget
+template <int NG> struct Unroll { static constexpr int value = NG <= 2 ? 4 : (NG <= 4 ? 2 : 1); };
+
 template <typename T, int NG>
-__device__ __forceinline__ void grad4(const MtaArgs& a, int t, int64_t e, float (&g)[4]) {
-  ld4(reinterpret_cast<const T*>(sec_grad(a, 0)[t]) + e, g);
-  if (NG == 0) {
+__device__ __forceinline__ void grad4(const MtaArgs& a, const T* const* gp, int t, int64_t e,
+                                      float (&g)[4]) {
+  if constexpr (NG == 1) {
+    ld4(gp[0] + e, g);
+  } else if constexpr (NG == 0) {
+    ld4(reinterpret_cast<const T*>(sec_grad(a, 0)[t]) + e, g);
     for (int i = 1; i < a.ngrad; i += 4) {
       float s[4];
       ld4(reinterpret_cast<const T*>(sec_grad(a, i)[t]) + e, s);
@@ -95,12 +102,30 @@ __device__ __forceinline__ void grad4(const MtaArgs& a, int t, int64_t e, float 
 #pragma unroll
       for (int j = 0; j < 4; ++j) g[j] = add_as<T>(g[j], s[j]);
     }
+  } else {
+    // all NG loads (local or NVLink peer memory) are issued back to back, then summed in order
+    float x[NG][4];
+#pragma unroll
+    for (int k = 0; k < NG; ++k) ld4(gp[k] + e, x[k]);
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      float acc = x[0][j];
+#pragma unroll
+      for (int i = 1; i < NG; i += 4) {
+        float sum = x[i][j];
+#pragma unroll
+        for (int k = 1; k < 4; ++k)
+          if (i + k < NG) sum = add_as<T>(sum, x[i + k][j]);
+        acc = add_as<T>(acc, sum);
+      }
+      g[j] = acc;
+    }
   }
 }
 template <typename T, int NG>
 __device__ __forceinline__ float grad1(const MtaArgs& a, int t, int64_t e) {
   float g = ld1(reinterpret_cast<const T*>(sec_grad(a, 0)[t]) + e);
-  if (NG == 0) {
+  if (NG != 1) {
     for (int i = 1; i < a.ngrad; i += 4) {
       float s = ld1(reinterpret_cast<const T*>(sec_grad(a, i)[t]) + e);
       for (int k = 1; k < 4 && i + k < a.ngrad; ++k)
@@ -305,9 +330,12 @@ mta_kernel(const MtaArgs a, const Op op, const float* __restrict__ gscale,
     if (F.read_w || F.write_w) bits |= (reinterpret_cast<uint64_t>(wp) + oW) * mW;
     if (F.read_s0 || F.write_s0) bits |= reinterpret_cast<uint64_t>(s0p) + o4;
     if (F.read_s1 || F.write_s1) bits |= reinterpret_cast<uint64_t>(s1p) + o4;
+    constexpr int NGC = NG > 0 ? NG : 1;
+    const T* gp[NGC];
     if (F.read_g) {
-      const int ng = NG == 0 ? a.ngrad : 1;
-      for (int k = 0; k < ng; ++k) bits |= (sec_grad(a, k)[t] + oT) * mT;
+#pragma unroll
+      for (int k = 0; k < NGC; ++k) gp[k] = reinterpret_cast<const T*>(sec_grad(a, k)[t]);
+      for (int k = 0; k < a.ngrad; ++k) bits |= (sec_grad(a, k)[t] + oT) * mT;
     }
     if (F.write_out)
       for (int k = 0; k < a.nout; ++k) bits |= (sec_out(a, k)[t] + oT) * mT;
@@ -315,21 +343,23 @@ mta_kernel(const MtaArgs a, const Op op, const float* __restrict__ gscale,
 
     if (vec) {
       const int nvec = ch.len >> 2;
-      float w[kU][4], g[kU][4], s0[kU][4], s1[kU][4];
+      constexpr int U = Unroll<NG>::value;
+      for (int v0 = 0; v0 < nvec; v0 += U * kThreads) {
+      float w[U][4], g[U][4], s0[U][4], s1[U][4];
 #pragma unroll
-      for (int u = 0; u < kU; ++u) {
-        const int v = u * kThreads + tid;
+      for (int u = 0; u < U; ++u) {
+        const int v = v0 + u * kThreads + tid;
         if (v < nvec) {
           const int64_t e = base + 4 * v;
-          if (F.read_g) grad4<T, NG>(a, t, e, g[u]);
+          if (F.read_g) grad4<T, NG>(a, gp, t, e, g[u]);
           if (F.read_w) ld4(wp + e, w[u]);
           if (F.read_s0) ld4(s0p + e, s0[u]);
           if (F.read_s1) ld4(s1p + e, s1[u]);
         }
       }
 #pragma unroll
-      for (int u = 0; u < kU; ++u) {
-        const int v = u * kThreads + tid;
+      for (int u = 0; u < U; ++u) {
+        const int v = v0 + u * kThreads + tid;
         if (v < nvec) {
           const int64_t e = base + 4 * v;
 #pragma unroll
@@ -343,6 +373,7 @@ mta_kernel(const MtaArgs a, const Op op, const float* __restrict__ gscale,
           if (F.write_out)
             for (int k = 0; k < a.nout; ++k) st4(reinterpret_cast<T*>(sec_out(a, k)[t]) + e, w[u]);
         }
+      }
       }
     }
     // scalar path: the <4-element tail of a vector chunk, or the whole chunk when unaligned
@@ -381,6 +412,48 @@ mta_kernel(const MtaArgs a, const Op op, const float* __restrict__ gscale,
       __syncthreads();
     }
   }
+}
+
+// ------------------------------------------------------------------------------------------------
+// Cross-GPU barriers for the peer-memory (NVLink) path.  Every rank owns a flag block
+// [ready[8] | done[8]] that its peers write with system-scope stores; `flags[k]` is rank k's block
+// as mapped into this process (cudaIpcOpenMemHandle), flags[rank] the local one.
+//   ready: "my gradient bucket for step `epoch` is complete — you may read your shard of it"
+//   done : "I have written my shard of the new weights into your weight buffer"
+// Each kernel is one warp: lane k signals rank k, then waits for rank k's signal.  The ranks run
+// on different GPUs, so waiting here cannot starve the signaller.  A bounded spin (~20 s) turns a
+// lost peer into an error flag instead of a hung GPU.
+// ------------------------------------------------------------------------------------------------
+struct P2PFlags {
+  uint32_t* flags[kMaxCopies];
+  int world, rank;
+  uint32_t epoch;
+};
+
+__device__ __forceinline__ void st_release_sys(uint32_t* p, uint32_t v) {
+  asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t* p) {
+  uint32_t v;
+  asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+
+// which = 0: ready slots, 1: done slots.  flags block layout: [0..8) ready, [8..16) done, [16] error
+static __global__ void p2p_barrier_kernel(const P2PFlags f, int which) {
+  const int k = threadIdx.x;
+  if (k >= f.world) return;
+  __threadfence_system();
+  st_release_sys(f.flags[k] + which * 8 + f.rank, f.epoch);
+  const uint32_t* mine = f.flags[f.rank] + which * 8 + k;
+  const long long t0 = clock64();
+  while (static_cast<int32_t>(ld_acquire_sys(mine) - f.epoch) < 0) {
+    if (clock64() - t0 > 40000000000LL) {   // ~20 s at 2 GHz: give up rather than hang the GPU
+      f.flags[f.rank][16] = 1;
+      break;
+    }
+  }
+  __threadfence_system();
 }
 
 // second stage of the deterministic reduction: one warp per tensor sums that tensor's chunk

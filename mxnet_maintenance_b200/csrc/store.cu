@@ -6,6 +6,7 @@
 
 #include <algorithm>
 #include <cmath>
+#include <cstdlib>
 #include <cstring>
 
 #include "nccl_dl.h"
@@ -440,6 +441,14 @@ void Store::run_class(Mode mode, DensePlan& p, const std::vector<const Entry*>& 
     s.gbuf.reserve(static_cast<size_t>(s.total) * es);
     CUDA_OK(cudaMemsetAsync(s.gbuf.p, 0, static_cast<size_t>(s.total) * es, stream_));
   }
+  if (push && has_opt() && p.full_segment) {
+    if (!s.p2p.tried) setup_p2p(s);
+    if (s.p2p.ok) {
+      ring_.end(stream_);   // hand the (unused) slot back; the peer path carves its own
+      run_class_p2p(p, s, ents, pull);
+      return;
+    }
+  }
   if (push) {
     Blob b(host + o_pack, nt, ng, 0);
     for (int t = 0; t < nt; ++t) {
@@ -468,8 +477,11 @@ void Store::run_class(Mode mode, DensePlan& p, const std::vector<const Entry*>& 
   if (push) {
     MtaCall c = base;
     c.blob = dev + o_pack; c.ngrad = ng; c.nout = 0; c.plan = &p.full;
+    prof_begin(1);
     launches_ += launch_copy(c, true, false);   // user gradients (local copies summed) -> fusion bucket
+    prof_end();
     if (has_opt()) {
+      prof_begin(2);
       if (p.full_segment) {
         NCCL_OK(nccl->ReduceScatter(s.gbuf.p, at(s.gbuf, rank_ * s.slice, es), s.slice, nt_type, ncclSum,
                                     comm, stream_));
@@ -480,12 +492,14 @@ void Store::run_class(Mode mode, DensePlan& p, const std::vector<const Entry*>& 
                                pc.root, comm, stream_));
         NCCL_OK(nccl->GroupEnd());
       }
+      prof_end();
       MtaCall u = base;
       u.blob = dev + o_upd; u.ngrad = upd_ng; u.nout = upd_no; u.plan = &p.shard;
       prof_begin();
       const float* gscale = opt_.clip_global_norm >= 0.f ? global_norm_scale(p, p.shard, u) : nullptr;
       update_chunks(p, p.shard, u, gscale);
       prof_end();
+      prof_begin(3);
       if (p.full_segment) {
         NCCL_OK(nccl->AllGather(at(s.wbuf, rank_ * s.slice, es), s.wbuf.p, s.slice, nt_type, comm, stream_));
       } else {
@@ -495,6 +509,7 @@ void Store::run_class(Mode mode, DensePlan& p, const std::vector<const Entry*>& 
                                   comm, stream_));
         NCCL_OK(nccl->GroupEnd());
       }
+      prof_end();
     } else {
       // no updater: all-reduce the merged gradients straight into the stored values
       if (p.full_segment) {
@@ -513,7 +528,174 @@ void Store::run_class(Mode mode, DensePlan& p, const std::vector<const Entry*>& 
   if (pull) {
     MtaCall c = base;
     c.blob = dev + o_unpack; c.ngrad = 1; c.nout = no; c.plan = &p.full;
+    prof_begin(4);
     launches_ += launch_copy(c, false, true);
+    prof_end();
+  }
+  ring_.end(stream_);
+}
+
+// ---- peer-memory path --------------------------------------------------------------------------------
+// Map every rank's gradient bucket, weight buffer and flag block into this process (CUDA IPC over
+// NVLink peer access).  All ranks must agree on the outcome, so the result is min-reduced.
+void Store::setup_p2p(Segment& s) {
+  s.p2p.tried = true;
+  const char* env = getenv("B200KV_P2P");
+  if (env && env[0] == '0') return;
+  if (world_ > kMaxCopies) return;
+  Segment::P2P& P = s.p2p;
+  NcclApi& nccl = NcclApi::get();
+  ncclComm_t comm = reinterpret_cast<ncclComm_t>(comm_);
+  struct Handles { cudaIpcMemHandle_t g, w, f; };
+  P.local_flags.reserve(2u << 20);   // its own 2 MiB allocation: IPC maps whole allocations
+  CUDA_OK(cudaMemsetAsync(P.local_flags.p, 0, 256, stream_));
+  Handles mine;
+  int ok = 1;
+  if (cudaIpcGetMemHandle(&mine.g, s.gbuf.p) != cudaSuccess) ok = 0;
+  if (cudaIpcGetMemHandle(&mine.w, s.wbuf.p) != cudaSuccess) ok = 0;
+  if (cudaIpcGetMemHandle(&mine.f, P.local_flags.p) != cudaSuccess) ok = 0;
+  (void)cudaGetLastError();
+  DevBuf stage;
+  const size_t hb = sizeof(Handles);
+  stage.reserve(hb * world_ + 64);
+  char* sp = stage.as<char>();
+  CUDA_OK(cudaMemcpyAsync(sp + hb * rank_, &mine, hb, cudaMemcpyHostToDevice, stream_));
+  NCCL_OK(nccl.AllGather(sp + hb * rank_, sp, hb, ncclChar, comm, stream_));
+  std::vector<Handles> all(world_);
+  CUDA_OK(cudaMemcpyAsync(all.data(), sp, hb * world_, cudaMemcpyDeviceToHost, stream_));
+  CUDA_OK(cudaStreamSynchronize(stream_));
+  for (int k = 0; k < world_ && ok; ++k) {
+    if (k == rank_) {
+      P.g[k] = s.gbuf.p; P.w[k] = s.wbuf.p; P.flags[k] = P.local_flags.as<uint32_t>();
+      continue;
+    }
+    void* f = nullptr;
+    if (cudaIpcOpenMemHandle(&P.g[k], all[k].g, cudaIpcMemLazyEnablePeerAccess) != cudaSuccess ||
+        cudaIpcOpenMemHandle(&P.w[k], all[k].w, cudaIpcMemLazyEnablePeerAccess) != cudaSuccess ||
+        cudaIpcOpenMemHandle(&f, all[k].f, cudaIpcMemLazyEnablePeerAccess) != cudaSuccess)
+      ok = 0;
+    P.flags[k] = static_cast<uint32_t*>(f);
+  }
+  (void)cudaGetLastError();
+  // agreement: the peer path is used only if every rank mapped every peer
+  int* flag = reinterpret_cast<int*>(sp + hb * world_);
+  CUDA_OK(cudaMemcpyAsync(flag, &ok, sizeof(int), cudaMemcpyHostToDevice, stream_));
+  NCCL_OK(nccl.AllReduce(flag, flag, 1, ncclInt, ncclMin, comm, stream_));
+  int agreed = 0;
+  CUDA_OK(cudaMemcpyAsync(&agreed, flag, sizeof(int), cudaMemcpyDeviceToHost, stream_));
+  CUDA_OK(cudaStreamSynchronize(stream_));
+  P.ok = agreed == 1;
+  if (!P.ok)
+    for (int k = 0; k < world_; ++k) {
+      if (k == rank_) continue;
+      if (P.g[k]) cudaIpcCloseMemHandle(P.g[k]);
+      if (P.w[k]) cudaIpcCloseMemHandle(P.w[k]);
+      if (P.flags[k]) cudaIpcCloseMemHandle(P.flags[k]);
+      P.g[k] = P.w[k] = nullptr; P.flags[k] = nullptr;
+    }
+}
+
+// One fused kernel per step does reduce-scatter + update + all-gather over peer memory: the rank's
+// shard of every peer's gradient bucket is read through NVLink and summed in rank order with the
+// reference's CommCPU grouping (=> same bits as the CPU reference for any number of GPUs), the
+// optimizer runs on the shard, and the new weights are stored into every peer's weight buffer.
+void Store::run_class_p2p(DensePlan& p, Segment& s, const std::vector<const Entry*>& ents, bool pull) {
+  const int nt = static_cast<int>(p.keys.size());
+  const size_t es = dtype_size(s.dtype);
+  const bool mp = use_mp(s);
+  const int W = world_;
+  Segment::P2P& P = s.p2p;
+  const int ng = p.ngrad, no = pull ? p.nout : 0;
+  // LAMB and global-norm clipping make several passes over the merged gradient: reduce the shard
+  // into the local bucket once instead of crossing NVLink on every pass
+  const bool prereduce = opt_.kind == B200KV_OPT_LAMB || opt_.clip_global_norm >= 0.f;
+  const int upd_ng = prereduce ? 1 : W, upd_no = mp ? W : W - 1;
+  const size_t w_pack = mta_blob_words(nt, ng, 0), w_pre = prereduce ? mta_blob_words(nt, W, 0) : 0,
+               w_upd = mta_blob_words(nt, upd_ng, upd_no), w_unpack = mta_blob_words(nt, 1, no);
+  uint64_t* host = ring_.begin((w_pack + w_pre + w_upd + w_unpack) * 8);
+  const size_t o_pack = 0, o_pre = w_pack, o_upd = o_pre + w_pre, o_unpack = o_upd + w_upd;
+  {
+    Blob b(host + o_pack, nt, ng, 0);
+    for (int t = 0; t < nt; ++t) {
+      for (int k = 0; k < ng; ++k) b.G(k, t, ents[t]->vals[k].data);
+      b.S(kSecW, t, at(s.gbuf, keys_[p.keys[t]].off, es));
+    }
+  }
+  if (prereduce) {
+    Blob b(host + o_pre, nt, W, 0);
+    for (int t = 0; t < nt; ++t) {
+      const int64_t off = keys_[p.keys[t]].off;
+      for (int k = 0; k < W; ++k) b.G(k, t, static_cast<char*>(P.g[k]) + off * es);
+      b.S(kSecW, t, at(s.gbuf, off, es));
+    }
+  }
+  {
+    Blob u(host + o_upd, nt, upd_ng, upd_no);
+    for (int t = 0; t < nt; ++t) {
+      const KeyInfo& ki = keys_[p.keys[t]];
+      if (prereduce) u.G(0, t, at(s.gbuf, ki.off, es));
+      else for (int k = 0; k < W; ++k) u.G(k, t, static_cast<char*>(P.g[k]) + ki.off * es);
+      int o = 0;
+      for (int k = 0; k < W; ++k) {
+        if (!mp && k == rank_) continue;   // fp32: the W section already is the local weight buffer
+        u.O(o++, t, static_cast<char*>(P.w[k]) + ki.off * es);
+      }
+      u.S(kSecW, t, mp ? at(s.master, ki.off - s.state_begin, 4) : at(s.wbuf, ki.off, 4));
+      if (s.has_s0) u.S(kSecS0, t, at(s.s0, ki.off - s.state_begin, 4));
+      if (s.has_s1) u.S(kSecS1, t, at(s.s1, ki.off - s.state_begin, 4));
+      u.F2(kSecLrWd, t, ki.lr, ki.wd);
+      if (opt_.kind == B200KV_OPT_LAMB) {
+        const float tf = static_cast<float>(ki.step);
+        u.F2(kSecAux, t, 1.0f - powf(opt_.beta1, tf), 1.0f - powf(opt_.beta2, tf));
+      }
+    }
+  }
+  if (pull) {
+    Blob b(host + o_unpack, nt, 1, no);
+    for (int t = 0; t < nt; ++t) {
+      b.G(0, t, at(s.wbuf, keys_[p.keys[t]].off, es));
+      for (int k = 0; k < no; ++k) b.O(k, t, ents[t]->outs[k].data);
+    }
+  }
+  const uint64_t* dev = ring_.commit(stream_);
+  MtaCall base;
+  base.nt = nt; base.dtype = s.dtype; base.stream = stream_; base.device = device_;
+
+  MtaCall c = base;
+  c.blob = dev + o_pack; c.ngrad = ng; c.nout = 0; c.plan = &p.full;
+  prof_begin(1);
+  launches_ += launch_copy(c, true, false);
+  prof_end();
+
+  P2PFlagsHost f;
+  for (int k = 0; k < kMaxCopies; ++k) f.flags[k] = P.flags[k];
+  f.world = W; f.rank = rank_; f.epoch = ++P.epoch;
+  prof_begin(2);
+  launches_ += launch_p2p_barrier(f, 0, stream_);       // every rank's bucket is complete
+  if (prereduce) {
+    MtaCall r = base;
+    r.blob = dev + o_pre; r.ngrad = W; r.nout = 0; r.plan = &p.shard;
+    launches_ += launch_copy(r, true, false);
+  }
+  prof_end();
+
+  MtaCall u = base;
+  u.blob = dev + o_upd; u.ngrad = upd_ng; u.nout = upd_no; u.plan = &p.shard;
+  prof_begin(0);
+  const float* gscale = opt_.clip_global_norm >= 0.f ? global_norm_scale(p, p.shard, u) : nullptr;
+  update_chunks(p, p.shard, u, gscale);
+  prof_end();
+
+  prof_begin(3);
+  launches_ += launch_p2p_barrier(f, 1, stream_);       // every rank's shard has landed everywhere
+  prof_end();
+
+  if (pull) {
+    MtaCall q = base;
+    q.blob = dev + o_unpack; q.ngrad = 1; q.nout = no; q.plan = &p.full;
+    prof_begin(4);
+    launches_ += launch_copy(q, false, true);
+    prof_end();
   }
   ring_.end(stream_);
 }
@@ -633,14 +815,16 @@ void Store::run_bound(int id) {
 void Store::unbind(int id) { bound_.erase(id); }
 
 // ---- kernel timing ---------------------------------------------------------------------------------
-void Store::prof_begin() {
+void Store::prof_begin(int phase) {
   if (!profiling_) return;
   if (prof_used_ == prof_events_.size()) {
     cudaEvent_t a, b;
     CUDA_OK(cudaEventCreate(&a));
     CUDA_OK(cudaEventCreate(&b));
     prof_events_.emplace_back(a, b);
+    prof_phase_.push_back(0);
   }
+  prof_phase_[prof_used_] = phase;
   CUDA_OK(cudaEventRecord(prof_events_[prof_used_].first, stream_));
 }
 
@@ -650,18 +834,25 @@ void Store::prof_end() {
   ++prof_used_;
 }
 
-void Store::profile_read(double* ms, int64_t* count) {
+void Store::profile_read_phases(double ms[8], int64_t count[8]) {
   use_device();
   CUDA_OK(cudaStreamSynchronize(stream_));
-  double total = 0;
+  for (int i = 0; i < 8; ++i) { ms[i] = 0; count[i] = 0; }
   for (size_t i = 0; i < prof_used_; ++i) {
     float t = 0;
     CUDA_OK(cudaEventElapsedTime(&t, prof_events_[i].first, prof_events_[i].second));
-    total += t;
+    ms[prof_phase_[i] & 7] += t;
+    count[prof_phase_[i] & 7] += 1;
   }
-  *ms = total;
-  *count = static_cast<int64_t>(prof_used_);
   prof_used_ = 0;
+}
+
+void Store::profile_read(double* ms, int64_t* count) {
+  double m[8];
+  int64_t c[8];
+  profile_read_phases(m, c);
+  *ms = m[0];
+  *count = c[0];
 }
 
 // ---- optimizer state access (checkpointing) --------------------------------------------------------

@@ -42,6 +42,15 @@ struct Segment {
   int64_t state_begin = 0, state_len = 0;  // element range the state arrays cover
   bool has_s0 = false, has_s1 = false, has_master = false;
   bool w_stale = false;  // world == 1 && master: wbuf lags behind master (pull casts the master)
+  // peer-memory (NVLink) path: every rank's gbuf / wbuf / flag block mapped into this process
+  struct P2P {
+    bool tried = false, ok = false;
+    void* g[kMaxCopies] = {nullptr};
+    void* w[kMaxCopies] = {nullptr};
+    uint32_t* flags[kMaxCopies] = {nullptr};
+    DevBuf local_flags;
+    uint32_t epoch = 0;
+  } p2p;
 };
 
 struct DensePlan {
@@ -79,6 +88,8 @@ class Store {
   // CUDA-event timing of the update kernels (bench.py's roofline leg)
   void set_profiling(bool on) { profiling_ = on; }
   void profile_read(double* ms, int64_t* count);
+  // per phase: 0 update, 1 pack, 2 reduce(-scatter), 3 all-gather / broadcast, 4 unpack
+  void profile_read_phases(double ms[8], int64_t count[8]);
   void set_optimizer(const b200kv_optimizer& opt);
   void set_hyper(int num, const int* keys, const float* lrs, const float* wds, const int* steps);
   float last_global_norm();
@@ -117,7 +128,7 @@ class Store {
   void prepare(Mode mode, int vnum, const int* vkeys, DLManagedTensor* const* vals, int onum,
                const int* okeys, DLManagedTensor* const* outs, BoundCall* bc, bool allow_staged);
   void execute(BoundCall& bc);
-  void prof_begin();
+  void prof_begin(int phase = 0);
   void prof_end();
   KeyInfo& info(int key);
   void use_device();
@@ -130,6 +141,8 @@ class Store {
   void update_chunks(DensePlan& p, const ChunkPlan& cp, const MtaCall& call, const float* gscale);
   const float* global_norm_scale(DensePlan& p, const ChunkPlan& cp, const MtaCall& gcall);
   void set_hyper_rsp(int key, float lr, float wd, int step);
+  void setup_p2p(Segment& s);
+  void run_class_p2p(DensePlan& p, Segment& s, const std::vector<const Entry*>& ents, bool pull);
   bool has_opt() const { return opt_.kind != B200KV_OPT_NONE; }
   bool use_mp(const Segment& s) const { return s.dtype == kF16 && opt_.multi_precision != 0; }
 
@@ -153,6 +166,7 @@ class Store {
   int next_bound_ = 1;
   bool profiling_ = false;
   std::vector<std::pair<cudaEvent_t, cudaEvent_t>> prof_events_;
+  std::vector<int> prof_phase_;
   size_t prof_used_ = 0;
 };
 

@@ -366,6 +366,13 @@ class B200(KVStoreBase):
         check_call(self._lib.b200kv_profile_read(self._h, C.byref(ms), C.byref(n)))
         return ms.value, n.value
 
+    def profile_read_phases(self):
+        """{phase: (ms, count)} since the last read; phases: update, pack, reduce, gather, unpack."""
+        ms, n = (C.c_double * 8)(), (C.c_int64 * 8)()
+        check_call(self._lib.b200kv_profile_read_phases(self._h, ms, n))
+        names = ["update", "pack", "reduce", "gather", "unpack"]
+        return {names[i]: (ms[i], n[i]) for i in range(5)}
+
     def broadcast(self, key, value, out, priority=0):
         """kvstore.py:98-118 / base.py:77-95: init with rank 0's value, then pull into `out`."""
         vkeys, vals, use_str = _flatten(key, value)

@@ -1,0 +1,345 @@
+// Row-sparse kernels for sm_100a, CUB-free:
+//   * LSD radix sort of (row id, source position) pairs, 8-bit digits, only ceil(log2(num_rows)/8)
+//     passes (the reference sorts full 64-bit keys with CUB, src/kvstore/kvstore_utils.cu:44-98)
+//   * head-flag scan -> sorted unique ids + segment starts (replaces cub::DeviceSelect::Unique and
+//     the O(num_rows) flag array + cub::DeviceScan of src/ndarray/ndarray_function.cu:104-190)
+//   * segmented row reduce in source order (= the reference's device-order accumulation,
+//     src/ndarray/ndarray_function.cc:81-113), optionally fused with the lazy row update
+//     (SGDMomDnsRspDnsKernel / AdamDnsRspDnsKernel, src/operator/optimizer_op-inl.h:747-802,1342-1409)
+//   * row gather for row_sparse_pull (SparseRetainRspThreadKernel, sparse_retain-inl.h:121-150)
+// Work is O(nnz), never O(num_rows).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "optim.cuh"
+
+namespace b200kv {
+
+constexpr int kSortTile = 4096;     // keys per CTA: 8 warps x 16 rounds x 32 lanes
+constexpr int kSortThreads = 256;
+constexpr int kScanTile = 1024;     // keys per CTA in the head-flag scan
+
+// ---- ids -> sort keys ------------------------------------------------------------------------------
+struct RspInputs {
+  const void* idx[kMaxCopies];   // row ids of each copy (int64 for pushes)
+  const float* val[kMaxCopies];  // row values of each copy
+  int64_t start[kMaxCopies + 1]; // position of each copy's first row in the concatenation
+  int n;                         // copies
+};
+
+// dtype: kI64 | kI32 | kF32 (row_ids given as float arrays hold integers, Appendix A.9)
+template <typename I>
+__device__ __forceinline__ uint32_t id_to_key(I v) { return static_cast<uint32_t>(static_cast<int64_t>(v)); }
+
+template <typename I>
+__global__ void make_keys_kernel(const RspInputs in, int64_t total, uint32_t* __restrict__ keys,
+                                 uint32_t* __restrict__ pay) {
+  for (int64_t i = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x; i < total;
+       i += static_cast<int64_t>(gridDim.x) * blockDim.x) {
+    int k = 0;
+    while (k + 1 < in.n && i >= in.start[k + 1]) ++k;
+    keys[i] = id_to_key(static_cast<const I*>(in.idx[k])[i - in.start[k]]);
+    pay[i] = static_cast<uint32_t>(i);
+  }
+}
+
+// ---- radix sort ------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(kSortThreads)
+radix_hist_kernel(const uint32_t* __restrict__ keys, int n, int shift, uint32_t* __restrict__ counts,
+                  int nblocks) {
+  __shared__ uint32_t hist[256];
+  hist[threadIdx.x] = 0;
+  __syncthreads();
+  const int base = blockIdx.x * kSortTile;
+  for (int i = threadIdx.x; i < kSortTile; i += kSortThreads) {
+    const int g = base + i;
+    if (g < n) atomicAdd(&hist[(keys[g] >> shift) & 255u], 1u);
+  }
+  __syncthreads();
+  counts[threadIdx.x * nblocks + blockIdx.x] = hist[threadIdx.x];
+}
+
+// exclusive scan of m values in place, one CTA of 1024 threads (m = 256 * nblocks, a few 10^4)
+__global__ void __launch_bounds__(1024) scan_small_kernel(uint32_t* __restrict__ v, int m) {
+  __shared__ uint32_t wsum[32];
+  const int tid = threadIdx.x;
+  const int per = (m + 1023) / 1024;
+  const int b = tid * per, e = min(b + per, m);
+  uint32_t s = 0;
+  for (int i = b; i < e; ++i) s += v[i];
+  // block-wide exclusive scan of s
+  uint32_t x = s;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    const uint32_t y = __shfl_up_sync(0xffffffffu, x, o);
+    if ((tid & 31) >= o) x += y;
+  }
+  if ((tid & 31) == 31) wsum[tid >> 5] = x;
+  __syncthreads();
+  if (tid < 32) {
+    uint32_t w = wsum[tid];
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const uint32_t y = __shfl_up_sync(0xffffffffu, w, o);
+      if (tid >= o) w += y;
+    }
+    wsum[tid] = w;
+  }
+  __syncthreads();
+  uint32_t run = x - s + ((tid >> 5) ? wsum[(tid >> 5) - 1] : 0u);
+  for (int i = b; i < e; ++i) {
+    const uint32_t t = v[i];
+    v[i] = run;
+    run += t;
+  }
+}
+
+// stable scatter: rank of a key = #equal digits before it (global offset of its CTA + earlier
+// warps of the CTA + earlier positions inside its warp segment, by __match_any_sync)
+__global__ void __launch_bounds__(kSortThreads)
+radix_scatter_kernel(const uint32_t* __restrict__ keys_in, const uint32_t* __restrict__ pay_in,
+                     uint32_t* __restrict__ keys_out, uint32_t* __restrict__ pay_out, int n, int shift,
+                     const uint32_t* __restrict__ offsets, int nblocks) {
+  __shared__ uint32_t wcount[kSortThreads / 32][256];
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  for (int i = tid; i < (kSortThreads / 32) * 256; i += kSortThreads) (&wcount[0][0])[i] = 0;
+  __syncthreads();
+  constexpr int kRounds = kSortTile / kSortThreads;   // 16
+  const int base = blockIdx.x * kSortTile + warp * (kRounds * 32);
+  uint32_t key[kRounds];
+  uint16_t rank[kRounds];
+  const uint32_t lt = (1u << lane) - 1u;
+#pragma unroll
+  for (int r = 0; r < kRounds; ++r) {
+    const int i = base + r * 32 + lane;
+    const bool valid = i < n;
+    key[r] = valid ? keys_in[i] : 0u;
+    const uint32_t d = valid ? ((key[r] >> shift) & 255u) : 256u;   // invalid lanes match each other only
+    const uint32_t mask = __match_any_sync(0xffffffffu, d);
+    const uint32_t before = __popc(mask & lt);
+    uint32_t prev = 0;
+    if (valid) prev = wcount[warp][d];
+    __syncwarp();
+    if (valid && before == 0) wcount[warp][d] = prev + __popc(mask);
+    __syncwarp();
+    rank[r] = static_cast<uint16_t>(prev + before);
+  }
+  __syncthreads();
+  {  // digit `tid`: exclusive prefix over the warps, seeded with this CTA's global offset
+    uint32_t run = offsets[tid * nblocks + blockIdx.x];
+#pragma unroll
+    for (int w = 0; w < kSortThreads / 32; ++w) {
+      const uint32_t t = wcount[w][tid];
+      wcount[w][tid] = run;
+      run += t;
+    }
+  }
+  __syncthreads();
+#pragma unroll
+  for (int r = 0; r < kRounds; ++r) {
+    const int i = base + r * 32 + lane;
+    if (i < n) {
+      const uint32_t pos = wcount[warp][(key[r] >> shift) & 255u] + rank[r];
+      keys_out[pos] = key[r];
+      pay_out[pos] = pay_in[i];
+    }
+  }
+}
+
+// ---- unique: head-flag scan ------------------------------------------------------------------------
+__device__ __forceinline__ bool is_head(const uint32_t* keys, int i) {
+  return i == 0 || keys[i] != keys[i - 1];
+}
+
+__global__ void __launch_bounds__(256)
+head_count_kernel(const uint32_t* __restrict__ keys, int n, uint32_t* __restrict__ bsum) {
+  __shared__ uint32_t ws[8];
+  const int base = blockIdx.x * kScanTile;
+  uint32_t c = 0;
+  for (int j = threadIdx.x; j < kScanTile; j += 256) {
+    const int i = base + j;
+    if (i < n && is_head(keys, i)) ++c;
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) c += __shfl_down_sync(0xffffffffu, c, o);
+  if ((threadIdx.x & 31) == 0) ws[threadIdx.x >> 5] = c;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    uint32_t t = 0;
+    for (int w = 0; w < 8; ++w) t += ws[w];
+    bsum[blockIdx.x] = t;
+  }
+}
+
+// after scan_small_kernel(bsum): bsum[b] = heads before tile b; count[0] = total number of heads
+__global__ void __launch_bounds__(256)
+head_write_kernel(const uint32_t* __restrict__ keys, int n, const uint32_t* __restrict__ bsum,
+                  int64_t* __restrict__ uniq, int32_t* __restrict__ seg_start, int64_t* __restrict__ count,
+                  int nb) {
+  __shared__ uint32_t ws[8];
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int i0 = blockIdx.x * kScanTile + tid * 4;   // 4 consecutive keys per thread
+  bool h[4];
+  uint32_t c = 0;
+#pragma unroll
+  for (int j = 0; j < 4; ++j) {
+    h[j] = (i0 + j < n) && is_head(keys, i0 + j);
+    c += h[j];
+  }
+  uint32_t x = c;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    const uint32_t y = __shfl_up_sync(0xffffffffu, x, o);
+    if (lane >= o) x += y;
+  }
+  if (lane == 31) ws[warp] = x;
+  __syncthreads();
+  uint32_t pos = bsum[blockIdx.x] + x - c;
+  for (int w = 0; w < warp; ++w) pos += ws[w];
+#pragma unroll
+  for (int j = 0; j < 4; ++j)
+    if (h[j]) {
+      uniq[pos] = static_cast<int64_t>(keys[i0 + j]);
+      seg_start[pos] = i0 + j;
+      ++pos;
+    }
+  if (blockIdx.x == nb - 1 && tid == 255) {   // last thread of the last tile knows the total
+    seg_start[pos] = n;
+    count[0] = pos;
+  }
+}
+
+// ---- segmented row reduce (+ optional lazy update) ---------------------------------------------------
+enum RspMode { kRspStore = 0, kRspSgd = 1, kRspAdam = 2 };
+
+struct RspUpdate {
+  int mode;
+  float lr, wd, momentum, beta1, beta2, eps, rescale, clip;
+  int has_mom;
+  float* table;  // [num_rows, row_len]
+  float* s0;
+  float* s1;
+};
+
+__device__ __forceinline__ const float* rsp_row(const RspInputs& in, uint32_t p, int64_t row_len) {
+  int k = 0;
+  while (k + 1 < in.n && static_cast<int64_t>(p) >= in.start[k + 1]) ++k;
+  return in.val[k] + (static_cast<int64_t>(p) - in.start[k]) * row_len;
+}
+
+// one CTA per output row; threads stride over the row in float4 (row_len % 4 == 0) or scalars
+template <int MODE, bool VEC>
+__global__ void __launch_bounds__(128)
+rsp_reduce_kernel(const RspInputs in, const uint32_t* __restrict__ pay, const int32_t* __restrict__ seg_start,
+                  const int64_t* __restrict__ uniq, const int64_t* __restrict__ count, int64_t row_len,
+                  float* __restrict__ out_val, const RspUpdate up) {
+  const int64_t nrows = count[0];
+  for (int64_t r = blockIdx.x; r < nrows; r += gridDim.x) {
+    const int b = seg_start[r], e = seg_start[r + 1];
+    const int64_t row = uniq[r];
+    constexpr int W = VEC ? 4 : 1;
+    for (int64_t c = static_cast<int64_t>(threadIdx.x) * W; c < row_len; c += 128 * W) {
+      float acc[W];
+#pragma unroll
+      for (int j = 0; j < W; ++j) acc[j] = 0.f;   // out = 0, then += every source row in order
+      for (int s = b; s < e; ++s) {
+        const float* src = rsp_row(in, pay[s], row_len) + c;
+        float x[W];
+        if constexpr (VEC) {
+          const float4 v = *reinterpret_cast<const float4*>(src);
+          x[0] = v.x; x[1] = v.y; x[2] = v.z; x[3] = v.w;
+        } else {
+          x[0] = src[0];
+        }
+#pragma unroll
+        for (int j = 0; j < W; ++j) acc[j] = __fadd_rn(acc[j], x[j]);
+      }
+      if (MODE == kRspStore) {
+#pragma unroll
+        for (int j = 0; j < W; ++j) out_val[r * row_len + c + j] = acc[j];
+      } else {
+        const int64_t o = row * row_len + c;
+#pragma unroll
+        for (int j = 0; j < W; ++j) {
+          float w = up.table[o + j];
+          if (MODE == kRspSgd) {
+            // SGDMomDnsRspDnsKernel: rate = lr*wd; mom = momentum*mom - rate*w - lr*clip(rescale*g) | lr*rescale*g
+            float mom = up.has_mom ? up.s0[o + j] : 0.f;
+            const float a = __fmul_rn(up.momentum, mom);
+            const float bb = __fmul_rn(__fmul_rn(up.lr, up.wd), w);
+            const float cc = up.clip >= 0.f ? __fmul_rn(up.lr, clipf(__fmul_rn(up.rescale, acc[j]), up.clip))
+                                            : __fmul_rn(__fmul_rn(up.lr, up.rescale), acc[j]);
+            mom = __fsub_rn(__fsub_rn(a, bb), cc);
+            if (up.has_mom) up.s0[o + j] = mom;
+            up.table[o + j] = __fadd_rn(w, mom);
+          } else {
+            // AdamDnsRspDnsKernel<cpu>: note (1-beta2)*square(clip(g)) with clipping but
+            // (1-beta2)*g*g (left to right) without
+            float m = up.s0[o + j], v = up.s1[o + j];
+            float gr = __fadd_rn(__fmul_rn(acc[j], up.rescale), __fmul_rn(w, up.wd));
+            const float omb1 = __fsub_rn(1.f, up.beta1), omb2 = __fsub_rn(1.f, up.beta2);
+            if (up.clip >= 0.f) {
+              gr = clipf(gr, up.clip);
+              m = __fadd_rn(__fmul_rn(up.beta1, m), __fmul_rn(omb1, gr));
+              v = __fadd_rn(__fmul_rn(up.beta2, v), __fmul_rn(omb2, __fmul_rn(gr, gr)));
+            } else {
+              m = __fadd_rn(__fmul_rn(up.beta1, m), __fmul_rn(omb1, gr));
+              v = __fadd_rn(__fmul_rn(up.beta2, v), __fmul_rn(__fmul_rn(omb2, gr), gr));
+            }
+            up.s0[o + j] = m;
+            up.s1[o + j] = v;
+            up.table[o + j] = __fsub_rn(w, __fdiv_rn(__fmul_rn(up.lr, m), __fadd_rn(__fsqrt_rn(v), up.eps)));
+          }
+        }
+      }
+    }
+  }
+}
+
+// ---- row gather for row_sparse_pull ------------------------------------------------------------------
+// full != 0: the store holds every row (dense table); otherwise (src_idx, src_val) is a compact
+// row-sparse value and absent rows come back as zeros.
+template <bool VEC>
+__global__ void __launch_bounds__(128)
+rsp_gather_kernel(const int64_t* __restrict__ uniq, const int64_t* __restrict__ count, int64_t row_len,
+                  int full, const float* __restrict__ table, int64_t num_rows,
+                  const int64_t* __restrict__ src_idx, const float* __restrict__ src_val,
+                  const int64_t* __restrict__ src_nnr, int64_t* __restrict__ out_idx,
+                  float* __restrict__ out_val) {
+  const int64_t nrows = count[0];
+  for (int64_t r = blockIdx.x; r < nrows; r += gridDim.x) {
+    const int64_t id = uniq[r];
+    const float* src = nullptr;
+    if (full) {
+      if (id >= 0 && id < num_rows) src = table + id * row_len;
+    } else {
+      int64_t lo = 0, hi = src_nnr[0] - 1;
+      while (lo <= hi) {
+        const int64_t m = lo + (hi - lo) / 2;
+        const int64_t v = src_idx[m];
+        if (v == id) { src = src_val + m * row_len; break; }
+        if (v < id) lo = m + 1; else hi = m - 1;
+      }
+    }
+    if (threadIdx.x == 0) out_idx[r] = id;
+    float* dst = out_val + r * row_len;
+    if constexpr (VEC) {
+      for (int64_t c = static_cast<int64_t>(threadIdx.x) * 4; c < row_len; c += 512)
+        *reinterpret_cast<float4*>(dst + c) =
+            src ? *reinterpret_cast<const float4*>(src + c) : make_float4(0.f, 0.f, 0.f, 0.f);
+    } else {
+      for (int64_t c = threadIdx.x; c < row_len; c += 128) dst[c] = src ? src[c] : 0.f;
+    }
+  }
+}
+
+__global__ void copy_i64_kernel(const int64_t* __restrict__ src, int64_t* __restrict__ dst,
+                                const int64_t* __restrict__ count) {
+  const int64_t n = count[0];
+  for (int64_t i = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x; i < n;
+       i += static_cast<int64_t>(gridDim.x) * blockDim.x)
+    dst[i] = src[i];
+}
+
+}  // namespace b200kv

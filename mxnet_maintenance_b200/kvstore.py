@@ -284,7 +284,7 @@ class B200(KVStoreBase):
         dense_idx = [i for i, v in enumerate(vals) if not _is_rsp(v)]
         for i, v in enumerate(vals):
             if _is_rsp(v):
-                self._init_rsp(ck[i], v)
+                self._init_rsp(ck[i], v, keys[i])
         if dense_idx:
             dk = (C.c_int * len(dense_idx))(*[ck[i] for i in dense_idx])
             ptrs, keep = self._handles([vals[i] for i in dense_idx], False)
@@ -388,8 +388,16 @@ class B200(KVStoreBase):
             self._sizes[k] = _numel(v)
 
     # ------------------------------------------------------------------ row sparse
-    def _init_rsp(self, ckey, v):
-        raise B200KVError("row-sparse init needs a dense [num_rows, row_len] table: use init_row_sparse")
+    def _init_rsp(self, ckey, v, key):
+        """init with a row-sparse value: rows that are absent are zero rows of the table."""
+        dev = torch.device("cuda", self._device)
+        shape = tuple(v.shape)
+        table = torch.zeros(shape, dtype=torch.float32, device=dev)
+        if v.indices is not None and _numel(v.indices) > 0:
+            table[v.indices.to(dev).long()] = v.data.to(dev).reshape((-1,) + shape[1:])
+        ptrs, keep = self._handles([table], False)
+        check_call(self._lib.b200kv_init_rsp(self._h, ckey, ptrs[0]))
+        self._rsp_shapes[key] = shape
 
     def init_row_sparse(self, key, table):
         """Initialise a row-sparse key from the dense [num_rows, row_len] table holding all rows

@@ -1,0 +1,47 @@
+"""Pure-Python statement of the store's flat-segment layout and shard ownership (csrc/store.cu:
+``Store::seal`` / ``Store::plan_for``), used by tools that need to know which rank owns which
+elements (checkpoint re-sharding, the multi-rank tests) without a GPU.
+
+Layout rule: keys are laid out in init order, each starting on a 64-element boundary; the segment
+is padded to a multiple of ``world * 64`` elements and rank r owns ``[r*slice, (r+1)*slice)``.
+"""
+ALIGN = 64
+
+
+def align_up(x, a):
+    return (x + a - 1) // a * a
+
+
+def segment_layout(sizes, world):
+    """-> (offsets, total, slice) in elements."""
+    offs, off = [], 0
+    for n in sizes:
+        offs.append(off)
+        off = align_up(off + n, ALIGN)
+    total = align_up(max(off, ALIGN), world * ALIGN)
+    return offs, total, total // world
+
+
+def pieces(sizes, world):
+    """[(key index, rank, begin element inside the key, length)] — the (key ∩ owner-slice) pieces
+    the store reduces to / broadcasts from their owners."""
+    offs, total, sl = segment_layout(sizes, world)
+    out = []
+    for k, (o, n) in enumerate(zip(offs, sizes)):
+        for r in range(world):
+            lo, hi = max(o, r * sl), min(o + n, (r + 1) * sl)
+            if lo < hi:
+                out.append((k, r, lo - o, hi - lo))
+    return out
+
+
+def shard_ranges(sizes, world, rank):
+    """per key: (begin, end) element range inside the key owned by `rank` (may be empty)."""
+    offs, total, sl = segment_layout(sizes, world)
+    lo, hi = rank * sl, (rank + 1) * sl
+    res = []
+    for o, n in zip(offs, sizes):
+        b = min(max(lo - o, 0), n)
+        e = max(min(hi - o, n), b)
+        res.append((b, e))
+    return res

@@ -246,7 +246,7 @@ def adam_lr(lr, beta1, beta2, t):
     """Adam.update: lr *= sqrt(1-beta2^t)/(1-beta1^t) in Python doubles (optimizer.py:1616-1619)."""
     coef1 = 1.0 - beta1 ** t
     coef2 = 1.0 - beta2 ** t
-    return lr * math.sqrt(coef2) / coef1
+    return lr * (math.sqrt(coef2) / coef1)     # `lr *= math.sqrt(coef2)/coef1`
 
 
 class LocalStoreModel:

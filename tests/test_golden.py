@@ -22,7 +22,7 @@ def split(flat, dt=np.float32):
 
 def adam_lr(lr, b1, b2, t):
     import math
-    return lr * math.sqrt(1.0 - b2 ** t) / (1.0 - b1 ** t)
+    return lr * (math.sqrt(1.0 - b2 ** t) / (1.0 - b1 ** t))
 
 
 # ---------------------------------------------------------------- CPU: oracle vs golden

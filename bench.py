@@ -49,6 +49,9 @@ def parse():
     ap.add_argument("--e2e-steps", type=int, default=20)
     ap.add_argument("--cpu-steps", type=int, default=0, help="0 = pick a count that takes ~10-20 s")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-views", action="store_true",
+                    help="use caller-owned gradient/weight arrays (adds the pack / unpack / out copies) "
+                         "instead of zero-copy views into the store")
     return ap.parse_args()
 
 
@@ -259,6 +262,17 @@ def run_b200(args):
     outs = [[w] for w in weights]
     kv.broadcast(keys, weights, outs)
     kv.wait()
+    if not args.no_views:
+        # the framework's parameter / gradient arrays ARE the store's buffers (b200kv_view): no
+        # pack, unpack or second weight copy exists on the path
+        src_g = flat_g
+        weights = [kv.weight_view(k, s) for k, s in zip(keys, shp)]
+        grads = [kv.grad_view(k, s) for k, s in zip(keys, shp)]
+        for g, o, s in zip(grads, offs, shp):
+            g.copy_(src_g[o:o + shapes.numel(s)].view(s))
+        flat_w, flat_g = kv.segment_views(keys[0])
+        tot = flat_w.numel()
+        outs = [[w] for w in weights]
 
     def barrier():
         if world > 1:
@@ -380,6 +394,8 @@ def run_b200(args):
         "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": ms_step,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": dt, "data": "synthetic",
         "config": {"workload": desc, "optimizer": kind, "update_on_kvstore": True,
+                   "arrays": "caller-owned (pack/unpack copies)" if args.no_views else
+                             "zero-copy views into the store (b200kv_view)",
                    "l2": "working set %.0f MB per step exceeds the 126 MB L2; no flush needed"
                          % ((esz * 2 + (16 if kind != "sgd" else 8) + (4 if mp else 0)) * nelem / 1e6),
                    "parallelism": "dp%d reduce-scatter / sharded update / all-gather" % world if world > 1

@@ -141,6 +141,15 @@ int b200kv_set_hyper(b200kv_handle h, int num, const int* keys, const float* lrs
 /* after a push with clip_global_norm >= 0: the total gradient norm of that push (blocks) */
 int b200kv_last_global_norm(b200kv_handle h, float* out);
 
+/* Zero-copy views INTO the store (the mirror image of the DLPack hand-over, MXNDArrayFromDLPackEx,
+ * include/mxnet/c_api.h:1008-1025): which = 0 the stored weight of `key`, 1 the slot of `key` in
+ * the gradient fusion bucket, 2 / 3 the whole weight / gradient segment that holds `key` (1-D).
+ * A framework that makes its parameter and gradient arrays these views (mx.nd.from_dlpack) pays
+ * no pack / unpack copy at all: pushpull recognises arrays that already are the store's buffers.
+ * The returned DLManagedTensor is owned by the consumer (call its deleter once); the memory stays
+ * valid until b200kv_free.  All keys must have been initialised before the first view is taken. */
+int b200kv_view(b200kv_handle h, int key, int which, DLManagedTensor** out);
+
 /* optimizer-state access for Trainer.save_states/load_states (python/mxnet/kvstore/kvstore.py:641-690,
  * optimizer.py:2142-2160).  which: 0 = momentum/mean, 1 = var, 2 = fp32 master weight.
  * get: copies the key's state into `out` (fp32, same element count); *present = 0 if that state

@@ -55,6 +55,7 @@ SIGNATURES = {
     "b200kv_set_optimizer": [_VP, C.POINTER(OptimizerDesc)],
     "b200kv_set_hyper": [_VP, _I, _PI, _PF, _PF, _PI],
     "b200kv_last_global_norm": [_VP, _PF],
+    "b200kv_view": [_VP, _I, _I, _PVP],
     "b200kv_get_state": [_VP, _I, _I, _VP, _PI],
     "b200kv_set_state": [_VP, _I, _I, _VP],
     "b200kv_init_rsp": [_VP, _I, _VP],

@@ -177,6 +177,12 @@ int b200kv_last_global_norm(b200kv_handle h, float* out) {
   API_END();
 }
 
+int b200kv_view(b200kv_handle h, int key, int which, DLManagedTensor** out) {
+  API_BEGIN();
+  *out = S(h)->view(key, which);
+  API_END();
+}
+
 int b200kv_get_state(b200kv_handle h, int key, int which, DLManagedTensor* out, int* present) {
   API_BEGIN();
   S(h)->get_state(key, which, out, present);

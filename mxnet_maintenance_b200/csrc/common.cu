@@ -32,7 +32,7 @@ TensorView view_of(const DLManagedTensor* t, int device_id, const char* what) {
     v.shape[i] = d.shape[i];
     v.numel *= d.shape[i];
   }
-  if (d.strides != nullptr) {  // MXNet only accepts compact row-major (tensor_blob.h:116-137)
+  if (d.strides != nullptr && v.numel > 0) {  // MXNet only accepts compact row-major (tensor_blob.h:116-137)
     int64_t expect = 1;
     for (int i = d.ndim - 1; i >= 0; --i) {
       KV_CHECK(d.shape[i] <= 1 || d.strides[i] == expect, what << ": tensor is not compact row-major");

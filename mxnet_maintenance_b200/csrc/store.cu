@@ -396,7 +396,34 @@ void Store::run_class(Mode mode, DensePlan& p, const std::vector<const Entry*>& 
     }
   };
 
+  // Arrays that ARE the store's own buffers (b200kv_view) need no copy: a gradient that already
+  // lives in its bucket slot is not packed, an out that is the stored weight is not written twice.
+  bool g_alias = push && ng == 1, o_alias = pull && no == 1;
+  for (int t = 0; t < nt && (g_alias || o_alias); ++t) {
+    const int64_t off = keys_[p.keys[t]].off;
+    if (g_alias && (s.gbuf.p == nullptr || ents[t]->vals[0].data != at(s.gbuf, off, es))) g_alias = false;
+    if (o_alias && ents[t]->outs[0].data != at(s.wbuf, off, es)) o_alias = false;
+  }
   if (world_ == 1) {
+    if (push && has_opt() && o_alias) {
+      // the caller's weights are the stored weights: update in place, no separate out copy
+      Blob b(host + o_upd, nt, ng, mp ? 1 : 0);
+      for (int t = 0; t < nt; ++t) {
+        for (int k = 0; k < ng; ++k) b.G(k, t, ents[t]->vals[k].data);
+        if (mp) b.O(0, t, ents[t]->outs[0].data);
+      }
+      fill_update_scalars(b);
+      dev = ring_.commit(stream_);
+      MtaCall c = base;
+      c.blob = dev + o_upd; c.ngrad = ng; c.nout = mp ? 1 : 0; c.plan = &p.full;
+      prof_begin();
+      const float* gscale = opt_.clip_global_norm >= 0.f ? global_norm_scale(p, p.full, c) : nullptr;
+      update_chunks(p, p.full, c, gscale);
+      prof_end();
+      s.w_stale = false;   // wbuf was written as the (fp16) out, or is the fp32 weight itself
+      ring_.end(stream_);
+      return;
+    }
     if (push) {
       Blob b(host + o_upd, nt, ng, no);
       for (int t = 0; t < nt; ++t) {
@@ -445,7 +472,7 @@ void Store::run_class(Mode mode, DensePlan& p, const std::vector<const Entry*>& 
     if (!s.p2p.tried) setup_p2p(s);
     if (s.p2p.ok) {
       ring_.end(stream_);   // hand the (unused) slot back; the peer path carves its own
-      run_class_p2p(p, s, ents, pull);
+      run_class_p2p(p, s, ents, pull, g_alias, o_alias);
       return;
     }
   }
@@ -477,9 +504,11 @@ void Store::run_class(Mode mode, DensePlan& p, const std::vector<const Entry*>& 
   if (push) {
     MtaCall c = base;
     c.blob = dev + o_pack; c.ngrad = ng; c.nout = 0; c.plan = &p.full;
-    prof_begin(1);
-    launches_ += launch_copy(c, true, false);   // user gradients (local copies summed) -> fusion bucket
-    prof_end();
+    if (!g_alias) {
+      prof_begin(1);
+      launches_ += launch_copy(c, true, false);   // user gradients (local copies summed) -> fusion bucket
+      prof_end();
+    }
     if (has_opt()) {
       prof_begin(2);
       if (p.full_segment) {
@@ -525,7 +554,7 @@ void Store::run_class(Mode mode, DensePlan& p, const std::vector<const Entry*>& 
       }
     }
   }
-  if (pull) {
+  if (pull && !o_alias) {
     MtaCall c = base;
     c.blob = dev + o_unpack; c.ngrad = 1; c.nout = no; c.plan = &p.full;
     prof_begin(4);
@@ -599,7 +628,8 @@ void Store::setup_p2p(Segment& s) {
 // shard of every peer's gradient bucket is read through NVLink and summed in rank order with the
 // reference's CommCPU grouping (=> same bits as the CPU reference for any number of GPUs), the
 // optimizer runs on the shard, and the new weights are stored into every peer's weight buffer.
-void Store::run_class_p2p(DensePlan& p, Segment& s, const std::vector<const Entry*>& ents, bool pull) {
+void Store::run_class_p2p(DensePlan& p, Segment& s, const std::vector<const Entry*>& ents, bool pull,
+                          bool g_alias, bool o_alias) {
   const int nt = static_cast<int>(p.keys.size());
   const size_t es = dtype_size(s.dtype);
   const bool mp = use_mp(s);
@@ -663,9 +693,11 @@ void Store::run_class_p2p(DensePlan& p, Segment& s, const std::vector<const Entr
 
   MtaCall c = base;
   c.blob = dev + o_pack; c.ngrad = ng; c.nout = 0; c.plan = &p.full;
-  prof_begin(1);
-  launches_ += launch_copy(c, true, false);
-  prof_end();
+  if (!g_alias) {
+    prof_begin(1);
+    launches_ += launch_copy(c, true, false);
+    prof_end();
+  }
 
   P2PFlagsHost f;
   for (int k = 0; k < kMaxCopies; ++k) f.flags[k] = P.flags[k];
@@ -690,7 +722,7 @@ void Store::run_class_p2p(DensePlan& p, Segment& s, const std::vector<const Entr
   launches_ += launch_p2p_barrier(f, 1, stream_);       // every rank's shard has landed everywhere
   prof_end();
 
-  if (pull) {
+  if (pull && !o_alias) {
     MtaCall q = base;
     q.blob = dev + o_unpack; q.ngrad = 1; q.nout = no; q.plan = &p.full;
     prof_begin(4);
@@ -853,6 +885,48 @@ void Store::profile_read(double* ms, int64_t* count) {
   profile_read_phases(m, c);
   *ms = m[0];
   *count = c[0];
+}
+
+// ---- zero-copy views --------------------------------------------------------------------------------
+namespace {
+struct ViewBox {
+  DLManagedTensor t;
+  int64_t shape[1];
+};
+void view_deleter(DLManagedTensor* self) { delete reinterpret_cast<ViewBox*>(self->manager_ctx); }
+}  // namespace
+
+DLManagedTensor* Store::view(int key, int which) {
+  use_device();
+  KeyInfo& ki = info(key);
+  if (ki.seg < 0) seal();
+  Segment& s = *segs_[keys_[key].seg];
+  KV_CHECK(which >= 0 && which <= 3, "view selector must be 0..3");
+  const size_t es = dtype_size(s.dtype);
+  const bool grad = which == 1 || which == 3;
+  if (grad && s.gbuf.p == nullptr) {
+    s.gbuf.reserve(static_cast<size_t>(s.total) * es);
+    CUDA_OK(cudaMemsetAsync(s.gbuf.p, 0, static_cast<size_t>(s.total) * es, stream_));
+  }
+  KV_CHECK(!(which == 0 || which == 2) || !s.w_stale,
+           "weight views must be taken before the first multi-precision update");
+  ViewBox* b = new ViewBox();
+  const bool whole = which >= 2;
+  b->shape[0] = whole ? s.total : keys_[key].size;
+  DLTensor& d = b->t.dl_tensor;
+  d.data = at(grad ? s.gbuf : s.wbuf, whole ? 0 : keys_[key].off, es);
+  d.device.device_type = kDLCUDA;
+  d.device.device_id = device_;
+  d.ndim = 1;
+  d.dtype.code = kDLFloat;
+  d.dtype.bits = static_cast<uint8_t>(es * 8);
+  d.dtype.lanes = 1;
+  d.shape = b->shape;
+  d.strides = nullptr;
+  d.byte_offset = 0;
+  b->t.manager_ctx = b;
+  b->t.deleter = view_deleter;
+  return &b->t;
 }
 
 // ---- optimizer state access (checkpointing) --------------------------------------------------------

@@ -93,6 +93,9 @@ class Store {
   void set_optimizer(const b200kv_optimizer& opt);
   void set_hyper(int num, const int* keys, const float* lrs, const float* wds, const int* steps);
   float last_global_norm();
+  // zero-copy views into the store's own buffers (which: 0 weight of `key`, 1 gradient bucket slot
+  // of `key`, 2 the whole weight segment holding `key`, 3 the whole gradient bucket)
+  DLManagedTensor* view(int key, int which);
   void get_state(int key, int which, DLManagedTensor* out, int* present);
   void set_state(int key, int which, DLManagedTensor* in);
   void barrier();
@@ -142,7 +145,8 @@ class Store {
   const float* global_norm_scale(DensePlan& p, const ChunkPlan& cp, const MtaCall& gcall);
   void set_hyper_rsp(int key, float lr, float wd, int step);
   void setup_p2p(Segment& s);
-  void run_class_p2p(DensePlan& p, Segment& s, const std::vector<const Entry*>& ents, bool pull);
+  void run_class_p2p(DensePlan& p, Segment& s, const std::vector<const Entry*>& ents, bool pull,
+                     bool g_alias, bool o_alias);
   bool has_opt() const { return opt_.kind != B200KV_OPT_NONE; }
   bool use_mp(const Segment& s) const { return s.dtype == kF16 && opt_.multi_precision != 0; }
 

@@ -357,6 +357,28 @@ class B200(KVStoreBase):
                                                   C.byref(bid)))
         return BoundStep(self, bid.value, list(dict.fromkeys(vkeys)), (vals, outs, keep_v, keep_o))
 
+    def _view(self, key, which, shape=None):
+        ck = self._keys([key], isinstance(key, str))
+        p = C.c_void_p()
+        check_call(self._lib.b200kv_view(self._h, ck[0], which, C.byref(p)))
+        new = C.pythonapi.PyCapsule_New
+        new.restype, new.argtypes = C.py_object, [C.c_void_p, C.c_char_p, C.c_void_p]
+        t = torch.utils.dlpack.from_dlpack(new(p.value, b"dltensor", None))
+        return t.view(shape) if shape is not None else t
+
+    def weight_view(self, key, shape=None):
+        """The stored weight of `key` as a zero-copy tensor.  A framework whose parameter array IS
+        this view (MXNet: ``mx.nd.from_dlpack``) needs no pull copy: pushpull updates it in place."""
+        return self._view(key, 0, shape)
+
+    def grad_view(self, key, shape=None):
+        """The slot of `key` in the gradient fusion bucket; gradients written here need no pack copy."""
+        return self._view(key, 1, shape)
+
+    def segment_views(self, key):
+        """(whole weight segment, whole gradient bucket) holding `key`, as flat tensors."""
+        return self._view(key, 2), self._view(key, 3)
+
     def set_profiling(self, enable):
         check_call(self._lib.b200kv_set_profiling(self._h, int(bool(enable))))
 

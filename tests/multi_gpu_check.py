@@ -109,6 +109,42 @@ def main():
     run(None)                          # no optimizer: all-reduce, merged value assigned
     run(None, batch=False)
 
+    # zero-copy store views: no pack / unpack, same results
+    def run_views(kind):
+        rng_w = np.random.default_rng(78)
+        w0 = [rng_w.uniform(-1, 1, s).astype(np.float32) for s in shp]
+        lr = 1e-3 if kind == "lamb" else 0.05
+        O = {"sgd": mb.optimizer.SGD, "lamb": mb.optimizer.LAMB}[kind]
+        kw = dict(momentum=0.9) if kind == "sgd" else {}
+        kv = mb.create("b200")
+        kv.set_optimizer(O(learning_rate=lr, wd=0.01, rescale_grad=1.0 / 8, **kw))
+        od = dict(kind=kind, lr=lr, wd=0.01, rescale=1.0 / 8)
+        if kind == "sgd":
+            od["momentum"] = 0.9
+        model = LocalStoreModel(oracle, od)
+        kv.init(keys, [torch.from_numpy(w).cuda() for w in w0])
+        for k, w in zip(keys, w0):
+            model.init(k, w)
+        wv = [kv.weight_view(k, s) for k, s in zip(keys, shp)]
+        gv = [kv.grad_view(k, s) for k, s in zip(keys, shp)]
+        step_fn = kv.bind_pushpull(keys, gv, out=[[w] for w in wv])
+        for step in range(3):
+            allg = [[(np.random.default_rng(5000 * step + r).uniform(-1, 1, s) * 1e-2).astype(np.float32)
+                     for s in shp] for r in range(world)]
+            for d, h in zip(gv, allg[rank]):
+                d.copy_(torch.from_numpy(h))
+            step_fn()
+            kv.wait()
+            for k in keys:
+                merged = oracle.reduce_sum([allg[r][k].copy() for r in range(world)])
+                ref = model.pushpull(k, [merged])
+                got = wv[k].cpu().numpy()
+                ok = got.tobytes() == ref.tobytes() if kind == "sgd" else np.allclose(got, ref, rtol=1e-5, atol=1e-6)
+                if not ok:
+                    failures.append("views %s step %d key %d" % (kind, step, k))
+    run_views("sgd")
+    run_views("lamb")
+
     # sharded optimizer state gathers back to the full per-key arrays (checkpointing)
     kv2, model2 = run("sgd", steps=2)
     st = kv2._collect_states()

@@ -226,3 +226,53 @@ def test_bound_step_equals_pushpull(kind):
         assert opt.num_update == 4 and opt._index_update_count[0] == 4
     for a, b in zip(*res):
         assert a.tobytes() == b.tobytes()
+
+
+@pytest.mark.parametrize("kind,mp", [("sgd", False), ("sgd", True), ("adam", False), ("lamb", False)])
+def test_store_views_update_in_place(oracle, kind, mp):
+    """Arrays that are zero-copy views of the store (b200kv_view) take the copy-free path; results
+    must not change (bit-exact vs the oracle for SGD / Adam)."""
+    from oracle.oracle import LocalStoreModel
+    import mxnet_maintenance_b200 as mb
+    shp = _shapes("ragged")
+    keys = list(range(len(shp)))
+    rng = np.random.default_rng(21)
+    wdt = np.float16 if mp else np.float32
+    w0 = [rng.uniform(-1, 1, s).astype(np.float32).astype(wdt) for s in shp]
+    lr = 1e-3 if kind == "lamb" else 0.05
+    O = {"sgd": mb.optimizer.SGD, "adam": mb.optimizer.Adam, "lamb": mb.optimizer.LAMB}[kind]
+    kw = dict(momentum=0.9) if kind == "sgd" else {}
+    kv = mb.create("b200")
+    kv.set_optimizer(O(learning_rate=lr, wd=0.01, rescale_grad=0.5, multi_precision=mp, **kw))
+    od = dict(kind=kind, lr=lr, wd=0.01, rescale=0.5, multi_precision=mp)
+    if kind == "sgd":
+        od["momentum"] = 0.9
+    model = LocalStoreModel(oracle, od)
+    kv.init(keys, [torch.from_numpy(w).cuda() for w in w0])
+    for k, w in zip(keys, w0):
+        model.init(k, w)
+    wv = [kv.weight_view(k, s) for k, s in zip(keys, shp)]
+    gv = [kv.grad_view(k, s) for k, s in zip(keys, shp)]
+    for w, h in zip(wv, w0):
+        assert w.cpu().numpy().tobytes() == h.tobytes()      # the view shows the initial value
+    base = kv.launch_count()
+    for step in range(3):
+        g = [(rng.uniform(-1, 1, s) * 1e-2).astype(np.float32).astype(wdt) for s in shp]
+        for d, h in zip(gv, g):
+            d.copy_(torch.from_numpy(h))
+        kv.pushpull(keys, gv, out=[[w] for w in wv])
+        kv.wait()
+        for k in keys:
+            ref = model.pushpull(k, [g[k]])
+            got = wv[k].cpu().numpy()
+            if kind == "lamb":
+                np.testing.assert_allclose(got, ref, rtol=RTOL32, atol=ATOL32)
+            else:
+                assert got.tobytes() == ref.tobytes()
+    per_step = (kv.launch_count() - base) / 3
+    assert per_step <= (4 if kind == "lamb" else 1) + (1 if mp else 0)
+    # a plain pull still returns the stored value
+    out = [torch.empty_like(w) for w in wv]
+    kv.pull(keys, out=out)
+    for a, b in zip(out, wv):
+        assert torch.equal(a, b)

@@ -11,6 +11,8 @@ struct MtaCall {
   int dtype = kF32;                 // element type of grads / outs: kF32 | kF16
   cudaStream_t stream = nullptr;
   int device = 0;
+  // gradient copies are 16-byte aligned bucket slots on several GPUs: use the TMA-staged kernel
+  bool staged = false;
 };
 
 struct OptScalars {
@@ -41,6 +43,11 @@ struct P2PFlagsHost {
   uint32_t epoch;
 };
 int launch_p2p_barrier(const P2PFlagsHost& f, int which, cudaStream_t stream);
+
+// TMA-staged forms (staged.cu); -1 = not eligible, use the plain launcher
+int launch_sgd_staged(const MtaCall& c, bool has_mom, const OptScalars& s, const float* gscale);
+int launch_adam_staged(const MtaCall& c, const OptScalars& s, const float* gscale);
+int launch_copy_staged(const MtaCall& c);
 
 int launch_reduce_partials(const float* partials, const ChunkPlan& plan, int nred, float* sums,
                            cudaStream_t stream);

@@ -63,6 +63,10 @@ int launch_update(const MtaCall& c, const Op& op, const float* gscale, float* pa
 }  // namespace
 
 int launch_sgd(const MtaCall& c, bool has_mom, const OptScalars& s, const float* gscale) {
+  if (c.staged) {
+    const int r = launch_sgd_staged(c, has_mom, s, gscale);
+    if (r >= 0) return r;
+  }
   if (has_mom) {
     SgdOp<true> op{s.momentum, s.rescale, s.clip};
     return launch_update(c, op, gscale, nullptr);
@@ -72,6 +76,10 @@ int launch_sgd(const MtaCall& c, bool has_mom, const OptScalars& s, const float*
 }
 
 int launch_adam(const MtaCall& c, const OptScalars& s, const float* gscale) {
+  if (c.staged) {
+    const int r = launch_adam_staged(c, s, gscale);
+    if (r >= 0) return r;
+  }
   AdamOp op{s.beta1, s.beta2, s.eps, s.rescale, s.clip};
   return launch_update(c, op, gscale, nullptr);
 }
@@ -94,6 +102,10 @@ int launch_sumsq(const MtaCall& c, float* partials) {
 }
 
 int launch_copy(const MtaCall& c, bool to_w, bool to_out, bool w_is_f32) {
+  if (c.staged && to_w && !to_out && !w_is_f32) {
+    const int r = launch_copy_staged(c);
+    if (r >= 0) return r;
+  }
 #define GO(TW, TO)                                                                          \
   do {                                                                                      \
     CopyOp<TW, TO> op;                                                                      \

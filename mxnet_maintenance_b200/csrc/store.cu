@@ -639,6 +639,8 @@ void Store::run_class_p2p(DensePlan& p, Segment& s, const std::vector<const Entr
   // LAMB and global-norm clipping make several passes over the merged gradient: reduce the shard
   // into the local bucket once instead of crossing NVLink on every pass
   const bool prereduce = opt_.kind == B200KV_OPT_LAMB || opt_.clip_global_norm >= 0.f;
+  static const bool staged_env = [] { const char* e = getenv("B200KV_STAGED"); return !(e && e[0] == '0'); }();
+  const bool staged = staged_env;
   const int upd_ng = prereduce ? 1 : W, upd_no = mp ? W : W - 1;
   const size_t w_pack = mta_blob_words(nt, ng, 0), w_pre = prereduce ? mta_blob_words(nt, W, 0) : 0,
                w_upd = mta_blob_words(nt, upd_ng, upd_no), w_unpack = mta_blob_words(nt, 1, no);
@@ -706,13 +708,13 @@ void Store::run_class_p2p(DensePlan& p, Segment& s, const std::vector<const Entr
   launches_ += launch_p2p_barrier(f, 0, stream_);       // every rank's bucket is complete
   if (prereduce) {
     MtaCall r = base;
-    r.blob = dev + o_pre; r.ngrad = W; r.nout = 0; r.plan = &p.shard;
+    r.blob = dev + o_pre; r.ngrad = W; r.nout = 0; r.plan = &p.shard; r.staged = staged;
     launches_ += launch_copy(r, true, false);
   }
   prof_end();
 
   MtaCall u = base;
-  u.blob = dev + o_upd; u.ngrad = upd_ng; u.nout = upd_no; u.plan = &p.shard;
+  u.blob = dev + o_upd; u.ngrad = upd_ng; u.nout = upd_no; u.plan = &p.shard; u.staged = staged && !prereduce;
   prof_begin(0);
   const float* gscale = opt_.clip_global_norm >= 0.f ? global_norm_scale(p, p.shard, u) : nullptr;
   update_chunks(p, p.shard, u, gscale);

@@ -309,6 +309,7 @@ mta_kernel(const MtaArgs a, const Op op, const float* __restrict__ gscale,
   const int tid = threadIdx.x;
   const float gs = (F.read_g && gscale != nullptr) ? *gscale : 1.0f;
   const bool use_gs = F.read_g && gscale != nullptr;
+  float red[2] = {0.f, 0.f};
 
   for (int c = blockIdx.x; c < a.nchunks; c += gridDim.x) {
     const Chunk ch = a.chunks[c];
@@ -320,7 +321,6 @@ mta_kernel(const MtaArgs a, const Op op, const float* __restrict__ gscale,
     const float2 lrwd = *reinterpret_cast<const float2*>(&sec(a, kSecLrWd)[t]);
     const float2 aux = *reinterpret_cast<const float2*>(&sec(a, kSecAux)[t]);
     const typename Op::PT pt = op_prep(op, lrwd.x, lrwd.y, aux.x, aux.y, t);
-    float red[2] = {0.f, 0.f};
 
     // 16-byte alignment (8 for a 2-byte type) of every array at this chunk's first element
     uint64_t bits = 0;
@@ -394,22 +394,32 @@ mta_kernel(const MtaArgs a, const Op op, const float* __restrict__ gscale,
     }
 
     if (F.nred > 0) {
-      // warp shuffle, then shared memory across the 8 warps; fixed order => run-to-run identical
+      // A CTA keeps accumulating in registers while its next chunk belongs to the same tensor
+      // (writing 0 for this chunk) and reduces across the block only at the end of such a run:
+      // big tensors cost one block reduction per CTA instead of one per 16 KB chunk.  The
+      // assignment of chunks to CTAs is fixed, so results stay run-to-run identical.
+      const int cn = c + gridDim.x;
+      const bool run_continues = cn < a.nchunks && a.chunks[cn].tensor == t;
+      if (run_continues) {
+        if (tid < F.nred) partials[static_cast<size_t>(c) * F.nred + tid] = 0.f;
+      } else {
 #pragma unroll
-      for (int r = 0; r < F.nred; ++r) {
-        float x = red[r];
+        for (int r = 0; r < F.nred; ++r) {
+          float x = red[r];
 #pragma unroll
-        for (int o = 16; o > 0; o >>= 1) x += __shfl_down_sync(0xffffffffu, x, o);
-        if ((tid & 31) == 0) sred[r][tid >> 5] = x;
+          for (int o = 16; o > 0; o >>= 1) x += __shfl_down_sync(0xffffffffu, x, o);
+          if ((tid & 31) == 0) sred[r][tid >> 5] = x;
+          red[r] = 0.f;
+        }
+        __syncthreads();
+        if (tid < F.nred) {
+          float x = 0.f;
+#pragma unroll
+          for (int k = 0; k < kThreads / 32; ++k) x += sred[tid][k];
+          partials[static_cast<size_t>(c) * F.nred + tid] = x;
+        }
+        __syncthreads();
       }
-      __syncthreads();
-      if (tid < F.nred) {
-        float x = 0.f;
-#pragma unroll
-        for (int k = 0; k < kThreads / 32; ++k) x += sred[tid][k];
-        partials[static_cast<size_t>(c) * F.nred + tid] = x;
-      }
-      __syncthreads();
     }
   }
 }

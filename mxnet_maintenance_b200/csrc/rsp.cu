@@ -28,6 +28,8 @@ struct RspKey {
   DevBuf keys_a, keys_b, pay_a, pay_b, counts, bsum, seg_start, uniq, count;
   int64_t cap = 0;
   bool merged_valid = false;
+  // multi-rank exchange buffers: this rank's rows packed contiguously, and every rank's rows
+  DevBuf send_idx, send_val, recv_idx, recv_val, counts_dev;
   float lr = 0.01f, wd = 0.f;
   int step = 0;
 
@@ -124,7 +126,6 @@ void Store::push_rsp(int key, int ncopies, DLManagedTensor* const* idx, DLManage
   KV_CHECK(it != rsp_.end(), "key " << key << " has not been initialized as row_sparse");
   RspKey& k = *it->second;
   KV_CHECK(ncopies >= 1 && ncopies <= kMaxCopies, "between 1 and " << kMaxCopies << " copies per push");
-  KV_CHECK(world_ == 1, "row-sparse push across several GPUs is not built yet (dense keys are)");
   RspInputs in;
   std::memset(&in, 0, sizeof(in));
   int64_t total = 0;
@@ -144,6 +145,50 @@ void Store::push_rsp(int key, int ncopies, DLManagedTensor* const* idx, DLManage
   }
   in.n = n;
   in.start[n] = total;
+  if (world_ > 1) {
+    // Every rank holds the whole table (replicated), so the exchange is an all-gather of the
+    // ranks' (ids, rows); afterwards each rank reduces and updates identically.  Rank r's rows keep
+    // their device order and ranks are concatenated in rank order = the reference's device order.
+    KV_CHECK(comm_, "b200kv_comm_init has not been called");
+    NcclApi& nccl = NcclApi::get();
+    ncclComm_t comm = reinterpret_cast<ncclComm_t>(comm_);
+    k.counts_dev.reserve(8 * static_cast<size_t>(world_));
+    std::vector<int64_t> counts(world_, 0);
+    CUDA_OK(cudaMemcpyAsync(k.counts_dev.as<int64_t>() + rank_, &total, 8, cudaMemcpyHostToDevice, stream_));
+    NCCL_OK(nccl.AllGather(k.counts_dev.as<int64_t>() + rank_, k.counts_dev.p, 1, ncclInt64, comm, stream_));
+    CUDA_OK(cudaMemcpyAsync(counts.data(), k.counts_dev.p, 8 * static_cast<size_t>(world_),
+                            cudaMemcpyDeviceToHost, stream_));
+    CUDA_OK(cudaStreamSynchronize(stream_));
+    const int64_t maxn = std::max<int64_t>(*std::max_element(counts.begin(), counts.end()), 1);
+    const size_t rowb = 4 * static_cast<size_t>(k.row_len);
+    k.send_idx.reserve(8 * static_cast<size_t>(maxn));
+    k.send_val.reserve(rowb * static_cast<size_t>(maxn));
+    k.recv_idx.reserve(8 * static_cast<size_t>(maxn) * world_);
+    k.recv_val.reserve(rowb * static_cast<size_t>(maxn) * world_);
+    for (int c = 0; c < n; ++c) {
+      const int64_t cnt = in.start[c + 1] - in.start[c];
+      CUDA_OK(cudaMemcpyAsync(k.send_idx.as<int64_t>() + in.start[c], in.idx[c], 8 * static_cast<size_t>(cnt),
+                              cudaMemcpyDeviceToDevice, stream_));
+      CUDA_OK(cudaMemcpyAsync(k.send_val.as<char>() + rowb * in.start[c], in.val[c], rowb * static_cast<size_t>(cnt),
+                              cudaMemcpyDeviceToDevice, stream_));
+    }
+    NCCL_OK(nccl.AllGather(k.send_idx.p, k.recv_idx.p, maxn, ncclInt64, comm, stream_));
+    NCCL_OK(nccl.AllGather(k.send_val.p, k.recv_val.p, static_cast<size_t>(maxn) * k.row_len, ncclFloat32, comm,
+                           stream_));
+    std::memset(&in, 0, sizeof(in));
+    total = 0;
+    n = 0;
+    for (int r = 0; r < world_; ++r) {
+      if (counts[r] == 0) continue;
+      in.idx[n] = k.recv_idx.as<int64_t>() + static_cast<int64_t>(r) * maxn;
+      in.val[n] = k.recv_val.as<float>() + static_cast<int64_t>(r) * maxn * k.row_len;
+      in.start[n] = total;
+      total += counts[r];
+      ++n;
+    }
+    in.n = n;
+    in.start[n] = total;
+  }
   KV_CHECK(total < (int64_t(1) << 31), "too many rows in one push");
   k.reserve(total);
   k.merged_valid = false;

@@ -145,6 +145,40 @@ def main():
     run_views("sgd")
     run_views("lamb")
 
+    # row-sparse keys: every rank pushes 2 device copies; union-sum in (rank, device) order
+    def run_rsp(with_opt):
+        num_rows, row_len = 3000, 64
+        table = np.random.default_rng(3).uniform(-1, 1, (num_rows, row_len)).astype(np.float32)
+        kv = mb.create("b200")
+        if with_opt:
+            kv.set_optimizer(mb.optimizer.SGD(learning_rate=0.1, momentum=0.9, wd=1e-3, rescale_grad=0.5))
+        kv.init_row_sparse(0, torch.from_numpy(table if rank == 0 else table * 0).cuda())
+        ref, mom = table.copy(), np.zeros_like(table)
+        for step in range(2):
+            allg = []
+            for r in range(world):
+                rg = np.random.default_rng(900 * step + r)
+                for _ in range(2):
+                    idx = np.unique(rg.integers(0, num_rows, 400)).astype(np.int64)
+                    allg.append((r, idx, (rg.uniform(-1, 1, (len(idx), row_len)) * 1e-2).astype(np.float32)))
+            mine = [mb.RowSparse(torch.from_numpy(v).cuda(), torch.from_numpy(i).cuda(), (num_rows, row_len))
+                    for (r, i, v) in allg if r == rank]
+            kv.push(0, mine)
+            midx, mval = oracle.rsp_sum([(i, v) for (_, i, v) in allg])
+            if with_opt:
+                oracle.sgd_mom_rsp(ref, mom, midx, mval, 0.1, 1e-3, 0.9, 0.5)
+            else:
+                m = kv.rsp_merged(0)
+                if m.indices.cpu().numpy().tobytes() != midx.tobytes() or m.data.cpu().numpy().tobytes() != mval.tobytes():
+                    failures.append("rsp merged step %d" % step)
+        if with_opt:
+            out = mb.RowSparse(None, None, (0, 0))
+            kv.row_sparse_pull(0, out=out, row_ids=torch.arange(num_rows, device="cuda"))
+            if out.data.cpu().numpy().tobytes() != ref.tobytes():
+                failures.append("rsp lazy update")
+    run_rsp(False)
+    run_rsp(True)
+
     # sharded optimizer state gathers back to the full per-key arrays (checkpointing)
     kv2, model2 = run("sgd", steps=2)
     st = kv2._collect_states()

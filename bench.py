@@ -36,6 +36,9 @@ WORKLOADS = {
                        "C3 BERT-base fp16 grads + fp32 masters (199 arrays, 109,482,240 params): fused mp adam_update"),
     "bert_large": ("bert_large", "f32", "lamb", 28,
                    "C4 BERT-large (391 fp32 arrays, 335,141,888 params): multi_lamb_update + global-norm clip"),
+    "rsp": ("rsp", "f32", "sgd", 20,
+            "C5 row_sparse embedding gradients (1,048,576 x 512 table, 65,536 Zipf ids per GPU with duplicates): "
+            "ReduceRowSparse + lazy sgd_mom_update + row_sparse_pull"),
 }
 
 
@@ -214,6 +217,146 @@ class Clocks:
         s = sorted(self.samples)
         return {"sm_mhz": (s[len(s) // 2] if s else None), "sm_max_mhz": self.max_mhz,
                 "reasons": sorted(self.reasons), "samples": len(s)}
+
+
+# ------------------------------------------------------------------------------------------------
+# C5: row-sparse push (+ lazy update) and row_sparse_pull
+# ------------------------------------------------------------------------------------------------
+def rsp_inputs(rank, step, num_rows, row_len, nids):
+    rng = np.random.default_rng(1234 + 1000 * step + rank)
+    raw = np.minimum(rng.zipf(1.05, nids) - 1, num_rows - 1).astype(np.int64)
+    idx = np.unique(raw)
+    val = (rng.uniform(-1, 1, (len(idx), row_len)) * 1e-2).astype(np.float32)
+    pull_ids = np.minimum(rng.zipf(1.05, nids) - 1, num_rows - 1).astype(np.int64)
+    return idx, val, pull_ids
+
+
+def run_rsp_cpu(args, world, steps):
+    from mxnet_maintenance_b200 import shapes
+    from oracle.oracle import Oracle
+    num_rows, row_len = shapes.ROW_SPARSE_TABLE
+    cores = os.cpu_count() or 1
+    o = Oracle("port", nthread=cores)
+    table = np.zeros((num_rows, row_len), np.float32)
+    mom = np.zeros_like(table)
+    ins = [rsp_inputs(r, 0, num_rows, row_len, shapes.ROW_SPARSE_IDS) for r in range(world)]
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        midx, mval = o.rsp_sum([(i, v) for i, v, _ in ins])
+        o.sgd_mom_rsp(table, mom, midx, mval, 0.1, 1e-4, 0.9)
+        for _, _, pid in ins:
+            u = o.unique(pid)
+            out = table[u]          # full table: SparseRetainCopyRetainedRowsFromDns (direct row copy)
+    return steps / (time.perf_counter() - t0), cores
+
+
+def run_rsp(args):
+    import torch
+    import torch.distributed as dist
+    import mxnet_maintenance_b200 as mb
+    from mxnet_maintenance_b200 import shapes
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    num_rows, row_len = shapes.ROW_SPARSE_TABLE
+    nids = shapes.ROW_SPARSE_IDS
+    kv = mb.create("b200")
+    kv.set_optimizer(mb.optimizer.SGD(learning_rate=0.1, momentum=0.9, wd=1e-4))
+    kv.init_row_sparse(0, torch.zeros((num_rows, row_len), device=dev))
+    nvar = 4   # rotate through a few input sets so consecutive steps differ
+    sets = []
+    for s in range(nvar):
+        idx, val, pid = rsp_inputs(rank, s, num_rows, row_len, nids)
+        sets.append((mb.RowSparse(torch.from_numpy(val).to(dev), torch.from_numpy(idx).to(dev), (num_rows, row_len)),
+                     torch.from_numpy(pid).to(dev), len(idx)))
+    out = mb.RowSparse(None, None, (0, 0))
+
+    def step(i):
+        g, pid, _ = sets[i % nvar]
+        kv.push(0, [g])
+        kv.row_sparse_pull(0, out=out, row_ids=pid)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+    clocks = Clocks(local) if rank == 0 else None
+    for i in range(max(args.warmup, 3)):
+        step(i)
+    barrier()
+    l0 = kv.launch_count()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    if clocks:
+        clocks.active = True
+    steps = min(args.steps, 100)
+    e0.record()
+    for i in range(steps):
+        step(i)
+    e1.record()
+    barrier()
+    if clocks:
+        clocks.active = False
+    ms = e0.elapsed_time(e1)
+    if world > 1:
+        t = torch.tensor([ms], device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = float(t.item())
+    launches = kv.launch_count() - l0
+    # e2e: host ids + rows in, pulled rows out
+    h = [(s[0].data.cpu().pin_memory(), s[0].indices.cpu().pin_memory(), s[1].cpu().pin_memory()) for s in sets]
+    def e2e_step(i):
+        v, ix, pid = h[i % nvar]
+        g = mb.RowSparse(v.to(dev, non_blocking=True), ix.to(dev, non_blocking=True), (num_rows, row_len))
+        kv.push(0, [g])
+        kv.row_sparse_pull(0, out=out, row_ids=pid.to(dev, non_blocking=True))
+        return out.data.cpu()
+    e2e_step(0)
+    barrier()
+    t0 = time.perf_counter()
+    for i in range(args.e2e_steps):
+        res = e2e_step(i)
+    barrier()
+    e2e_s = time.perf_counter() - t0
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+    ms_step = ms / steps
+    peak, peak_src = peaks()
+    nnr = float(np.mean([s[2] for s in sets]))
+    uniq_pull = float(np.mean([len(np.unique(s[1].cpu().numpy())) for s in sets]))
+    # algorithmic bytes: reduce reads nnr*(8+4L) per copy, lazy update 20 B per
+    # merged element, pull reads + writes U'*4L (+ ids)
+    alg = world * nnr * (8 + 4 * row_len) + 20.0 * (world * nnr * 0.8) * row_len + 2 * uniq_pull * 4 * row_len + 8 * nids
+    line = {
+        "metric": "grad-sync+update steps/s", "value": 1e3 / ms_step, "unit": "steps/s", "n_gpus": world,
+        "steps": steps, "warmup": max(args.warmup, 3), "ms_per_step": ms_step, "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": WORKLOADS["rsp"][4], "optimizer": "sgd momentum (lazy row update)",
+                   "rows_per_push_per_gpu": nnr, "unique_rows_pulled": uniq_pull,
+                   "l2": "touched rows (%.0f MB) fit the 126 MB L2 only partly; inputs rotate over %d sets"
+                         % (nnr * row_len * 4 * 3 / 1e6, nvar)},
+        "roofline": {"bound": "hbm", "achieved": alg / (ms_step * 1e-3) / 1e9, "peak": peak, "unit": "GB/s",
+                     "frac": alg / (ms_step * 1e-3) / 1e9 / peak, "traffic": None,
+                     "kernel": "radix sort + rsp_reduce_kernel<sgd> + rsp_gather_kernel (whole step)",
+                     "algorithmic_bytes_per_step": alg, "peak_source": peak_src,
+                     "note": "whole-step time incl. the row-count read-back that row_sparse_pull needs"},
+        "e2e": {"value": args.e2e_steps / e2e_s, "unit": "steps/s",
+                "h2d_bytes_per_step": int(nnr * (8 + 4 * row_len) + 8 * nids),
+                "d2h_bytes_per_step": int(uniq_pull * 4 * row_len), "steps": args.e2e_steps},
+        "gpu_launches": launches, "clocks": clocks.result() if clocks else None,
+    }
+    if not args.no_cpu_baseline and world == 1:
+        cs, cores = run_rsp_cpu(args, 1, 5)
+        line["cpu_baseline"] = {"value": cs, "unit": "steps/s", "cores": cores, "kind": "port",
+                                "sample": "5 steps: ElementwiseSumRsp + SGDMomDnsRspDnsKernel + Unique + row copy"}
+    print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
 
 
 # ------------------------------------------------------------------------------------------------
@@ -444,5 +587,7 @@ if __name__ == "__main__":
     a = parse()
     if a.impl == "reference":
         run_reference(a)
+    elif a.workload == "rsp":
+        run_rsp(a)
     else:
         run_b200(a)

@@ -86,17 +86,18 @@ void TableRing::end(cudaStream_t stream) {
 }
 
 // ---- ChunkPlan ---------------------------------------------------------------------------------
-void ChunkPlan::build(const std::vector<int64_t>& begin, const std::vector<int64_t>& end) {
+void ChunkPlan::build(const std::vector<int64_t>& begin, const std::vector<int64_t>& end, int chunk_elems) {
+  KV_CHECK(chunk_elems > 0 && chunk_elems <= kChunk && chunk_elems % 1024 == 0, "bad chunk size");
   nt = static_cast<int>(begin.size());
   std::vector<Chunk> ch;
   std::vector<int> fst(nt + 1, 0);
   for (int t = 0; t < nt; ++t) {
     fst[t] = static_cast<int>(ch.size());
-    for (int64_t o = begin[t]; o < end[t]; o += kChunk) {
+    for (int64_t o = begin[t]; o < end[t]; o += chunk_elems) {
       Chunk c;
       c.tensor = t;
       c.off = o;
-      c.len = static_cast<int32_t>(end[t] - o < kChunk ? end[t] - o : kChunk);
+      c.len = static_cast<int32_t>(end[t] - o < chunk_elems ? end[t] - o : chunk_elems);
       ch.push_back(c);
     }
   }

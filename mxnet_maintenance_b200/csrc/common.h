@@ -110,8 +110,9 @@ struct ChunkPlan {
   DevBuf first;    // int[nt + 1]
   int nchunks = 0;
   int nt = 0;
-  // ranges: per tensor [begin, end) element range to cover (relative to tensor element 0)
-  void build(const std::vector<int64_t>& begin, const std::vector<int64_t>& end);
+  // ranges: per tensor [begin, end) element range to cover (relative to tensor element 0);
+  // chunk_elems <= kChunk, a multiple of 1024
+  void build(const std::vector<int64_t>& begin, const std::vector<int64_t>& end, int chunk_elems = kChunk);
 };
 
 int sm_count(int device);

@@ -13,6 +13,10 @@ struct MtaCall {
   int device = 0;
   // gradient copies are 16-byte aligned bucket slots on several GPUs: use the TMA-staged kernel
   bool staged = false;
+  // in-kernel cross-GPU barriers (MtaArgs::sync*)
+  const P2PFlags* sync = nullptr;
+  uint32_t epoch = 0;
+  int sync_mode = 0;
 };
 
 struct OptScalars {

@@ -24,6 +24,14 @@ struct Chunk {          // 16 bytes
 // The table is one blob of 8-byte words laid out as consecutive sections of `nt` words each:
 //   grad[0..ngrad) | out[0..nout) | w | s0 | s1 | size | (lr,wd) | (aux0,aux1)
 // Pointers are per-tensor element-0 addresses; a section may hold nulls when unused.
+// Cross-GPU flag blocks of the peer-memory path (see optim.cuh): flags[k] is rank k's block
+// [ready[8] | done[8] | error | cta counter] as mapped into this process.
+struct P2PFlags {
+  uint32_t* flags[kMaxCopies];
+  int world, rank;
+  uint32_t epoch;
+};
+
 struct MtaArgs {
   const uint64_t* blob;
   const Chunk* chunks;
@@ -31,6 +39,12 @@ struct MtaArgs {
   int nt;
   int ngrad;
   int nout;
+  // optional in-kernel cross-GPU barriers: bit 0 = wait until every rank's gradient bucket is
+  // ready before the first load; bit 1 = after the last store signal "my shard has landed" and
+  // wait for every rank's signal
+  const P2PFlags* sync;
+  uint32_t epoch;
+  int sync_mode;
 };
 
 inline size_t mta_blob_words(int nt, int ngrad, int nout) {

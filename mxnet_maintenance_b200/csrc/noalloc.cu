@@ -121,6 +121,9 @@ extern "C" int b200kv_multi_sum_sq_static(int num, int dtype, const void* const*
     a.nt = num;
     a.ngrad = 1;
     a.nout = 0;
+    a.sync = nullptr;
+    a.epoch = 0;
+    a.sync_mode = 0;
     float* partials = reinterpret_cast<float*>(base + kOffPartials);
     // Nothing in the scratch has to start at zero: stage 1 writes partials[0, c) and stage 2 reads
     // exactly that range, so whatever an earlier call left behind is never observed.

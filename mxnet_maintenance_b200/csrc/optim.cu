@@ -30,6 +30,9 @@ MtaArgs args_of(const MtaCall& c) {
   a.nt = c.nt;
   a.ngrad = c.ngrad;
   a.nout = c.nout;
+  a.sync = c.sync;
+  a.epoch = c.epoch;
+  a.sync_mode = c.sync_mode;
   return a;
 }
 

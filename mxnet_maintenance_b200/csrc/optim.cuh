@@ -300,6 +300,26 @@ __device__ __forceinline__ typename Op::PT op_prep(const Op& op, float lr, float
 // partials: [nchunks][nred] per-chunk reduction outputs (deterministic two-stage reduction, like
 // multi_sum_sq.cu's no-atomics design, NEWS.md:795).
 // ------------------------------------------------------------------------------------------------
+__device__ __forceinline__ void st_release_sys(uint32_t* p, uint32_t v) {
+  asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t* p) {
+  uint32_t v;
+  asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+
+
+__device__ __forceinline__ void spin_until(const uint32_t* p, uint32_t epoch, uint32_t* err) {
+  const long long t0 = clock64();
+  while (static_cast<int32_t>(ld_acquire_sys(p) - epoch) < 0) {
+    if (clock64() - t0 > 40000000000LL) {   // ~20 s: give up rather than hang the GPU
+      *err = 1;
+      break;
+    }
+  }
+}
+
 template <class Op, typename T, typename WT, int NG>
 __global__ void __launch_bounds__(kThreads, 2)
 mta_kernel(const MtaArgs a, const Op op, const float* __restrict__ gscale,
@@ -310,6 +330,16 @@ mta_kernel(const MtaArgs a, const Op op, const float* __restrict__ gscale,
   const float gs = (F.read_g && gscale != nullptr) ? *gscale : 1.0f;
   const bool use_gs = F.read_g && gscale != nullptr;
   float red[2] = {0.f, 0.f};
+
+  if (a.sync != nullptr && (a.sync_mode & 1)) {
+    // every rank's gradient bucket must be complete before this rank reads its shard of it
+    const P2PFlags& f = *a.sync;
+    if (tid < f.world) {
+      if (blockIdx.x == 0) st_release_sys(f.flags[tid] + f.rank, a.epoch);
+      spin_until(f.flags[f.rank] + tid, a.epoch, f.flags[f.rank] + 16);
+    }
+    __syncthreads();
+  }
 
   for (int c = blockIdx.x; c < a.nchunks; c += gridDim.x) {
     const Chunk ch = a.chunks[c];
@@ -422,6 +452,28 @@ mta_kernel(const MtaArgs a, const Op op, const float* __restrict__ gscale,
       }
     }
   }
+
+  if (a.sync != nullptr && (a.sync_mode & 2)) {
+    // "my shard of the new weights has landed in every peer's buffer": the last CTA to finish
+    // signals every rank and waits for theirs, so the grid completes only when the whole
+    // all-gather has — the caller's next kernel may then read the weights / refill the bucket.
+    const P2PFlags& f = *a.sync;
+    __shared__ int s_last;
+    __threadfence_system();
+    __syncthreads();
+    if (tid == 0) {
+      uint32_t* counter = f.flags[f.rank] + 17;
+      const uint32_t prev = atomicAdd(counter, 1u);
+      s_last = prev == gridDim.x - 1;
+      if (s_last) *counter = 0;
+    }
+    __syncthreads();
+    if (s_last && tid < f.world) {
+      __threadfence_system();
+      st_release_sys(f.flags[tid] + 8 + f.rank, a.epoch);
+      spin_until(f.flags[f.rank] + 8 + tid, a.epoch, f.flags[f.rank] + 16);
+    }
+  }
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -434,21 +486,6 @@ mta_kernel(const MtaArgs a, const Op op, const float* __restrict__ gscale,
 // on different GPUs, so waiting here cannot starve the signaller.  A bounded spin (~20 s) turns a
 // lost peer into an error flag instead of a hung GPU.
 // ------------------------------------------------------------------------------------------------
-struct P2PFlags {
-  uint32_t* flags[kMaxCopies];
-  int world, rank;
-  uint32_t epoch;
-};
-
-__device__ __forceinline__ void st_release_sys(uint32_t* p, uint32_t v) {
-  asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
-}
-__device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t* p) {
-  uint32_t v;
-  asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
-  return v;
-}
-
 // which = 0: ready slots, 1: done slots.  flags block layout: [0..8) ready, [8..16) done, [16] error
 static __global__ void p2p_barrier_kernel(const P2PFlags f, int which) {
   const int k = threadIdx.x;
@@ -456,13 +493,7 @@ static __global__ void p2p_barrier_kernel(const P2PFlags f, int which) {
   __threadfence_system();
   st_release_sys(f.flags[k] + which * 8 + f.rank, f.epoch);
   const uint32_t* mine = f.flags[f.rank] + which * 8 + k;
-  const long long t0 = clock64();
-  while (static_cast<int32_t>(ld_acquire_sys(mine) - f.epoch) < 0) {
-    if (clock64() - t0 > 40000000000LL) {   // ~20 s at 2 GHz: give up rather than hang the GPU
-      f.flags[f.rank][16] = 1;
-      break;
-    }
-  }
+  spin_until(mine, f.epoch, f.flags[f.rank] + 16);
   __threadfence_system();
 }
 

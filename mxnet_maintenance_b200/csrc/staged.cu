@@ -257,6 +257,9 @@ int launch_staged_ng(const MtaCall& c, const Op& op, const float* gscale, float*
   a.nt = c.nt;
   a.ngrad = c.ngrad;
   a.nout = c.nout;
+  a.sync = nullptr;
+  a.epoch = 0;
+  a.sync_mode = 0;
   const int g = sm_count(c.device) * per_sm;
   const int grid = a.nchunks < g ? a.nchunks : g;
   kernel<<<grid, kThreads, smem, c.stream>>>(a, op, gscale, partials);

@@ -284,7 +284,14 @@ DensePlan& Store::plan_for(int seg, const std::vector<int>& keys, int ngrad, int
       }
   }
   p->full.build(b, e);
-  if (world_ > 1) p->shard.build(sb, se);
+  if (world_ > 1) {
+    // a small shard gets finer chunks so that the persistent CTAs stay balanced (a ResNet-50 shard
+    // at 8 GPUs is only ~780 chunks of 4096 elements for ~450 resident CTAs)
+    int64_t shard_elems = 0;
+    for (int t = 0; t < nt; ++t) shard_elems += se[t] - sb[t];
+    const int chunk = shard_elems / kChunk < 16 * static_cast<int64_t>(sm_count(device_)) ? 1024 : kChunk;
+    p->shard.build(sb, se, chunk);
+  }
   const int maxc = std::max(p->full.nchunks, p->shard.nchunks);
   p->partials.reserve(sizeof(float) * 2 * static_cast<size_t>(std::max(maxc, 1)));
   p->sums.reserve(sizeof(float) * (3 * static_cast<size_t>(nt) + 4));
@@ -298,6 +305,9 @@ const float* Store::global_norm_scale(DensePlan& p, const ChunkPlan& cp, const M
   // clip_global_norm (python/mxnet/gluon/utils.py:122-161) on the merged gradients of this push
   MtaCall c = gcall;
   c.plan = &cp;
+  c.sync = nullptr;      // reads the locally reduced bucket only: no cross-GPU barrier here
+  c.sync_mode = 0;
+  c.staged = false;
   float* partials = p.partials.as<float>();
   float* sums = p.sums.as<float>();
   launches_ += launch_sumsq(c, partials);
@@ -324,13 +334,16 @@ void Store::update_chunks(DensePlan& p, const ChunkPlan& cp, const MtaCall& call
       float* partials = p.partials.as<float>();
       float* sums = p.sums.as<float>();
       float* ratio = sums + 2 * static_cast<size_t>(c.nt);
-      launches_ += launch_lamb1(c, sc_, gscale, partials);
+      MtaCall c1 = c, c2 = c;
+      c1.sync_mode = c.sync_mode & 1;   // pass 1 is the first reader of the (peer) gradients
+      c2.sync_mode = c.sync_mode & 2;   // pass 2 is the last writer of the (peer) weights
+      launches_ += launch_lamb1(c1, sc_, gscale, partials);
       launches_ += launch_reduce_partials(partials, cp, 2, sums, stream_);
       if (world_ > 1)  // per-tensor norms span shards: one tiny all-reduce between the two passes
         NCCL_OK(NcclApi::get().AllReduce(sums, sums, 2 * static_cast<size_t>(c.nt), ncclFloat32, ncclSum,
                                          reinterpret_cast<ncclComm_t>(comm_), stream_));
       launches_ += launch_lamb_ratio(sums, c.nt, sc_.lower, sc_.upper, ratio, stream_);
-      launches_ += launch_lamb2(c, sc_, ratio);
+      launches_ += launch_lamb2(c2, sc_, ratio);
       break;
     }
     default:
@@ -614,6 +627,15 @@ void Store::setup_p2p(Segment& s) {
   CUDA_OK(cudaMemcpyAsync(&agreed, flag, sizeof(int), cudaMemcpyDeviceToHost, stream_));
   CUDA_OK(cudaStreamSynchronize(stream_));
   P.ok = agreed == 1;
+  if (P.ok) {
+    P2PFlags h;
+    std::memset(&h, 0, sizeof(h));
+    for (int k = 0; k < world_; ++k) h.flags[k] = P.flags[k];
+    h.world = world_;
+    h.rank = rank_;
+    P.dev_sync.reserve(sizeof(P2PFlags));
+    CUDA_OK(cudaMemcpy(P.dev_sync.p, &h, sizeof(h), cudaMemcpyHostToDevice));
+  }
   if (!P.ok)
     for (int k = 0; k < world_; ++k) {
       if (k == rank_) continue;
@@ -639,7 +661,7 @@ void Store::run_class_p2p(DensePlan& p, Segment& s, const std::vector<const Entr
   // LAMB and global-norm clipping make several passes over the merged gradient: reduce the shard
   // into the local bucket once instead of crossing NVLink on every pass
   const bool prereduce = opt_.kind == B200KV_OPT_LAMB || opt_.clip_global_norm >= 0.f;
-  static const bool staged_env = [] { const char* e = getenv("B200KV_STAGED"); return !(e && e[0] == '0'); }();
+  static const bool staged_env = [] { const char* e = getenv("B200KV_STAGED"); return e && e[0] == '1'; }();
   const bool staged = staged_env;
   const int upd_ng = prereduce ? 1 : W, upd_no = mp ? W : W - 1;
   const size_t w_pack = mta_blob_words(nt, ng, 0), w_pre = prereduce ? mta_blob_words(nt, W, 0) : 0,
@@ -704,25 +726,33 @@ void Store::run_class_p2p(DensePlan& p, Segment& s, const std::vector<const Entr
   P2PFlagsHost f;
   for (int k = 0; k < kMaxCopies; ++k) f.flags[k] = P.flags[k];
   f.world = W; f.rank = rank_; f.epoch = ++P.epoch;
+  // Barriers: folded into the first peer-reading / last peer-writing kernel (plain kernels), or
+  // separate one-warp kernels (TMA-staged kernels).
+  const bool fold = !staged;
+  const P2PFlags* dsync = P.dev_sync.as<P2PFlags>();
   prof_begin(2);
-  launches_ += launch_p2p_barrier(f, 0, stream_);       // every rank's bucket is complete
+  if (!fold) launches_ += launch_p2p_barrier(f, 0, stream_);       // every rank's bucket is complete
   if (prereduce) {
     MtaCall r = base;
     r.blob = dev + o_pre; r.ngrad = W; r.nout = 0; r.plan = &p.shard; r.staged = staged;
+    if (fold) { r.sync = dsync; r.epoch = f.epoch; r.sync_mode = 1; }
     launches_ += launch_copy(r, true, false);
   }
   prof_end();
 
   MtaCall u = base;
   u.blob = dev + o_upd; u.ngrad = upd_ng; u.nout = upd_no; u.plan = &p.shard; u.staged = staged && !prereduce;
+  if (fold) { u.sync = dsync; u.epoch = f.epoch; u.sync_mode = (prereduce ? 0 : 1) | 2; }
   prof_begin(0);
   const float* gscale = opt_.clip_global_norm >= 0.f ? global_norm_scale(p, p.shard, u) : nullptr;
   update_chunks(p, p.shard, u, gscale);
   prof_end();
 
-  prof_begin(3);
-  launches_ += launch_p2p_barrier(f, 1, stream_);       // every rank's shard has landed everywhere
-  prof_end();
+  if (!fold) {
+    prof_begin(3);
+    launches_ += launch_p2p_barrier(f, 1, stream_);       // every rank's shard has landed everywhere
+    prof_end();
+  }
 
   if (pull && !o_alias) {
     MtaCall q = base;

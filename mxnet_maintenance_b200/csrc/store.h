@@ -49,6 +49,7 @@ struct Segment {
     void* w[kMaxCopies] = {nullptr};
     uint32_t* flags[kMaxCopies] = {nullptr};
     DevBuf local_flags;
+    DevBuf dev_sync;     // P2PFlags resident on the device for the in-kernel barriers
     uint32_t epoch = 0;
   } p2p;
 };

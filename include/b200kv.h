@@ -232,6 +232,13 @@ int b200kv_multi_lamb_update(int num, int dtype, void* const* weights, const voi
 int b200kv_multi_sum_sq(int num, int dtype, const void* const* arrays, const int64_t* sizes,
                         float* out, void* stream);
 
+/* gluon.utils.clip_global_norm (python/mxnet/gluon/utils.py:122-161) as one fused sequence:
+ * total = sqrt(sum_i sum(x_i^2)); scale = min(max_norm / (total + 1e-8), 1); every array *= scale
+ * in place (rounded in the array dtype).  out_scale_norm: device pointer to two floats that
+ * receive {scale, total norm} — no host synchronisation (the reference blocks on .asscalar()). */
+int b200kv_clip_global_norm(int num, int dtype, void* const* arrays, const int64_t* sizes,
+                            float max_norm, float* out_scale_norm, void* stream);
+
 /* b200kv_multi_sum_sq_static — no counterpart in the reference.
  * Same result as b200kv_multi_sum_sq (bit for bit), for callers that cannot allocate device memory
  * while they run: a framework whose own pool has already taken the GPU's memory (a late cudaMalloc

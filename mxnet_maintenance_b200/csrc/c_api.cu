@@ -422,6 +422,36 @@ int b200kv_multi_lamb_update(int num, int dtype, void* const* weights, const voi
   API_END();
 }
 
+int b200kv_clip_global_norm(int num, int dtype, void* const* arrays, const int64_t* sizes,
+                            float max_norm, float* out_scale_norm, void* stream) {
+  API_BEGIN();
+  if (num <= 0) return 0;
+  const int dev = current_device();
+  OpWorkspace& w = workspace(dev);
+  std::lock_guard<std::mutex> lk(w.mu);
+  prepare_plan(w, num, sizes);
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  KV_CHECK(dtype == kF32 || dtype == kF16, "dtype must be 0 (float32) or 2 (float16)");
+  KV_CHECK(out_scale_norm != nullptr, "out_scale_norm must point to two device floats");
+  Table t{w.ring.begin(mta_blob_words(num, 1, 1) * 8), num, 1, 1};
+  std::memset(t.p, 0, mta_blob_words(num, 1, 1) * 8);
+  for (int i = 0; i < num; ++i) {
+    t.G(0, i, arrays[i]);
+    t.G(1, i, arrays[i]);   // the single out section follows the gradient section: scale in place
+  }
+  MtaCall c;
+  c.blob = w.ring.commit(st);
+  c.plan = &w.plan;
+  c.nt = num; c.ngrad = 1; c.nout = 1; c.dtype = dtype; c.stream = st; c.device = dev;
+  float* sums = w.sums.as<float>();
+  launch_sumsq(c, w.partials.as<float>());
+  launch_reduce_partials(w.partials.as<float>(), w.plan, 1, sums, st);
+  launch_global_norm(sums, num, max_norm, out_scale_norm, st);
+  launch_scale(c, out_scale_norm);
+  w.ring.end(st);
+  API_END();
+}
+
 int b200kv_multi_sum_sq(int num, int dtype, const void* const* arrays, const int64_t* sizes,
                         float* out, void* stream) {
   API_BEGIN();

@@ -37,6 +37,8 @@ int launch_sumsq(const MtaCall& c, float* partials);
 // W section <- sum of the G copies; optionally also to the out copies.  The W section holds
 // `dtype` elements, or fp32 when w_is_f32 (fp16 value -> fp32 master).
 int launch_copy(const MtaCall& c, bool to_w, bool to_out, bool w_is_f32 = false);
+// out copies <- G section * (*gscale), rounded in dtype (clip_global_norm's `arr *= scale`)
+int launch_scale(const MtaCall& c, const float* gscale);
 // out copies (dtype) <- W section (fp32 master)
 int launch_master_to_out(const MtaCall& c);
 

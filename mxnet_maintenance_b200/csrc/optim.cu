@@ -124,6 +124,13 @@ int launch_copy(const MtaCall& c, bool to_w, bool to_out, bool w_is_f32) {
 #undef GO
 }
 
+int launch_scale(const MtaCall& c, const float* gscale) {
+  CopyOp<false, true> op;
+  if (c.dtype == kF32) return launch_ng<CopyOp<false, true>, float, float>(c, op, gscale, nullptr);
+  KV_CHECK(c.dtype == kF16, "unsupported dtype " << c.dtype);
+  return launch_ng<CopyOp<false, true>, __half, __half>(c, op, gscale, nullptr);
+}
+
 int launch_master_to_out(const MtaCall& c) {
   MasterToOutOp op;
   KV_CHECK(c.dtype == kF16, "master_to_out is for fp16 outputs");

@@ -108,6 +108,23 @@ def multi_sum_sq(arrays):
     return out
 
 
+def clip_global_norm(arrays, max_norm):
+    """gluon.utils.clip_global_norm (python/mxnet/gluon/utils.py:122-161): rescales `arrays` in
+    place so that their global 2-norm is at most `max_norm`.  Returns a 2-element CUDA tensor
+    {scale, total_norm}; nothing is synchronised (read it with ``.cpu()`` when needed)."""
+    lib = _lib.load()
+    n = len(arrays)
+    for a in arrays:
+        assert a.is_cuda and a.is_contiguous()
+    out = torch.empty(2, dtype=torch.float32, device=arrays[0].device)
+    sizes = (C.c_int64 * n)(*[a.numel() for a in arrays])
+    stream = C.c_void_p(torch.cuda.current_stream(arrays[0].device).cuda_stream)
+    with torch.cuda.device(arrays[0].device):
+        check_call(lib.b200kv_clip_global_norm(n, _dtype_flag(arrays[0]), _pp(arrays), sizes, float(max_norm),
+                                               C.c_void_p(out.data_ptr()), stream))
+    return out
+
+
 STATIC_MAX_ARRAYS, STATIC_MAX_CHUNKS = 256, 16384
 
 

@@ -147,3 +147,23 @@ def test_cuda_lamb_and_sumsq_golden():
     # run-to-run determinism, bitwise (test_operator_gpu.py:281-283)
     ss2 = ops.multi_sum_sq(_cuda(split(G["sumsq_in"]))).cpu().numpy()
     assert ss.tobytes() == ss2.tobytes()
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("max_norm", [0.05, 1e6])
+def test_cuda_clip_global_norm(oracle, max_norm):
+    """ops.clip_global_norm vs the oracle's restatement of gluon.utils.clip_global_norm."""
+    from mxnet_maintenance_b200 import ops
+    rng = np.random.default_rng(9)
+    arrs = [(rng.uniform(-1, 1, s) * 1e-2).astype(np.float32) for s in (1, 77, 4096, 100003, 4097)]
+    dev = _cuda(arrs)
+    out = ops.clip_global_norm(dev, max_norm).cpu().numpy()
+    ref = [a.copy() for a in arrs]
+    total = oracle.clip_global_norm(ref, max_norm)
+    truth = float(np.sqrt(sum((a.astype(np.float64) ** 2).sum() for a in arrs)))
+    assert abs(out[1] - truth) <= 1e-6 * truth and abs(total - truth) <= 1e-5 * truth
+    for d, r in zip(dev, ref):
+        np.testing.assert_allclose(d.cpu().numpy(), r, rtol=1e-5, atol=1e-6)
+    if max_norm > 1:
+        for d, a in zip(dev, arrs):
+            assert d.cpu().numpy().tobytes() == a.tobytes()       # scale == 1: untouched bits

@@ -538,7 +538,10 @@ def run_b200(args):
         t_upd = float(bpe) * nelem / world / (peak * 1e9)
         ach_kernel = link_bytes / (k_ms * 1e-3) / 1e9
         ach_step = link_bytes / (ms_step * 1e-3) / 1e9
-        p2p_on = os.environ.get("B200KV_P2P", "1") != "0"
+        # single fused kernel (SGD / Adam on the peer-memory path): time that kernel; otherwise
+        # (NCCL path, or LAMB whose peer traffic is split over a reduce pass and the last update
+        # pass) the link bytes are spread over the step, so the step time is the denominator
+        p2p_on = os.environ.get("B200KV_P2P", "1") != "0" and kind != "lamb"
         roof = {"bound": "nvlink", "achieved": ach_kernel if p2p_on else ach_step, "peak": 770.0, "unit": "GB/s",
                 "frac": (ach_kernel if p2p_on else ach_step) / 770.0, "traffic": None,
                 "kernel": ("mta_kernel over peer memory: fused reduce-scatter + %s update + all-gather" % kind)

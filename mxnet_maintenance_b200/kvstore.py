@@ -366,6 +366,22 @@ class B200(KVStoreBase):
         t = torch.utils.dlpack.from_dlpack(new(p.value, b"dltensor", None))
         return t.view(shape) if shape is not None else t
 
+    def _view_capsule(self, key, which):
+        ck = self._keys([key], isinstance(key, str))
+        p = C.c_void_p()
+        check_call(self._lib.b200kv_view(self._h, ck[0], which, C.byref(p)))
+        new = C.pythonapi.PyCapsule_New
+        new.restype, new.argtypes = C.py_object, [C.c_void_p, C.c_char_p, C.c_void_p]
+        return new(p.value, b"dltensor", None)
+
+    def weight_view_capsule(self, key):
+        """DLPack capsule of the stored weight, for ``mx.nd.from_dlpack`` (1-D; reshape after)."""
+        return self._view_capsule(key, 0)
+
+    def grad_view_capsule(self, key):
+        """DLPack capsule of the key's gradient-bucket slot, for ``mx.nd.from_dlpack``."""
+        return self._view_capsule(key, 1)
+
     def weight_view(self, key, shape=None):
         """The stored weight of `key` as a zero-copy tensor.  A framework whose parameter array IS
         this view (MXNet: ``mx.nd.from_dlpack``) needs no pull copy: pushpull updates it in place."""

@@ -276,3 +276,82 @@ def test_store_views_update_in_place(oracle, kind, mp):
     kv.pull(keys, out=out)
     for a, b in zip(out, wv):
         assert torch.equal(a, b)
+
+
+def test_mixed_dtypes_late_init_and_optimizer_switch(oracle):
+    """One pushpull over fp16 and fp32 keys (BERT-style fp32 LayerNorm inside an fp16 model), keys
+    initialised after the first push (a second flat segment), and an optimizer change that resets
+    the state — each step compared with the oracle."""
+    from oracle.oracle import LocalStoreModel
+    import mxnet_maintenance_b200 as mb
+    rng = np.random.default_rng(31)
+    spec = [((300, 7), np.float16), ((64,), np.float32), ((4097,), np.float16), ((33,), np.float32)]
+    late = [((1000,), np.float32), ((129,), np.float16)]
+
+    def mk(shape, dt, scale=1.0):
+        return (rng.uniform(-1, 1, shape) * scale).astype(np.float32).astype(dt)
+
+    kv = mb.create("b200")
+    kv.set_optimizer(mb.optimizer.SGD(learning_rate=0.05, momentum=0.9, wd=1e-3, multi_precision=True))
+    model = LocalStoreModel(oracle, dict(kind="sgd", lr=0.05, momentum=0.9, wd=1e-3, multi_precision=True))
+    w = {}
+
+    def add(k, shape, dt):
+        h = mk(shape, dt)
+        model.init(k, h)
+        w[k] = torch.from_numpy(h).cuda()
+        kv.broadcast(k, w[k], out=[w[k]])
+
+    def step(keys, specs):
+        g = [mk(s, dt, 1e-2) for s, dt in specs]
+        kv.pushpull(keys, [torch.from_numpy(x).cuda() for x in g], out=[[w[k]] for k in keys])
+        kv.wait()
+        for k, x in zip(keys, g):
+            ref = model.pushpull(k, [x])
+            assert w[k].cpu().numpy().tobytes() == ref.tobytes(), "key %d" % k
+
+    for k, (s, dt) in enumerate(spec):
+        add(k, s, dt)
+    keys = list(range(len(spec)))
+    step(keys, spec)
+    step(keys, spec)
+    for j, (s, dt) in enumerate(late):           # new keys after the first push: a new segment
+        add(len(spec) + j, s, dt)
+    allkeys, allspec = keys + [4, 5], spec + late
+    step(allkeys, allspec)
+    step([5, 0, 3], [late[1], spec[0], spec[3]])   # a subset, out of order
+    # switching the optimizer resets the state (new Updater in the reference, kvstore.py:553-600)
+    kv.set_optimizer(mb.optimizer.Adam(learning_rate=1e-3, wd=0.01, multi_precision=True))
+    model.opt = dict(kind="adam", lr=1e-3, wd=0.01, multi_precision=True)
+    model.state, model.count = {}, {}
+    step(allkeys, allspec)
+    step(allkeys, allspec)
+    # and a pull still returns the stored (fp16 / fp32) values
+    outs = [torch.empty_like(w[k]) for k in allkeys]
+    kv.pull(allkeys, out=outs)
+    for k, o in zip(allkeys, outs):
+        assert torch.equal(o, w[k])
+
+
+def test_uneven_copy_counts_in_one_call(oracle):
+    """Keys with different numbers of device copies in the same pushpull (separate launch classes)."""
+    _, _, _ = None, None, None
+    from oracle.oracle import LocalStoreModel
+    import mxnet_maintenance_b200 as mb
+    rng = np.random.default_rng(32)
+    shp = [(100,), (5000,), (77, 3)]
+    ncop = [1, 3, 2]
+    kv = mb.create("b200")
+    kv.set_optimizer(mb.optimizer.SGD(learning_rate=0.1, momentum=0.9))
+    model = LocalStoreModel(oracle, dict(kind="sgd", lr=0.1, momentum=0.9))
+    w0 = [rng.uniform(-1, 1, s).astype(np.float32) for s in shp]
+    dev = [torch.from_numpy(x).cuda() for x in w0]
+    for k, x in enumerate(w0):
+        model.init(k, x)
+    kv.broadcast([0, 1, 2], dev, out=[[d] for d in dev])
+    for _ in range(2):
+        g = [[(rng.uniform(-1, 1, s) * 1e-2).astype(np.float32) for _ in range(n)] for s, n in zip(shp, ncop)]
+        kv.pushpull([0, 1, 2], [[torch.from_numpy(x).cuda() for x in gs] for gs in g], out=[[d] for d in dev])
+        kv.wait()
+        for k in range(3):
+            assert dev[k].cpu().numpy().tobytes() == model.pushpull(k, g[k]).tobytes()

@@ -437,12 +437,10 @@ def run_b200(args):
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     if clocks:
         clocks.active = True
-    t_host0 = time.perf_counter()
     e0.record()
     for _ in range(args.steps):
         step()
     e1.record()
-    t_host = time.perf_counter() - t_host0
     barrier()
     ms = e0.elapsed_time(e1)
     phases = kv.profile_read_phases()
@@ -519,8 +517,14 @@ def run_b200(args):
         alg = float(bpe) * nelem
         k_ms = kernel_ms / max(kernel_n, 1)
         ach = alg / (k_ms * 1e-3) / 1e9
+        traffic = None
+        tpath = os.path.join(ROOT, "profiles", "traffic_r1.json")
+        if os.path.exists(tpath) and not args.no_views:
+            with open(tpath) as f:
+                traffic = json.load(f).get(args.workload, {}).get("traffic")
         roof = {"bound": "hbm", "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
-                "traffic": None, "kernel": "mta_kernel (fused multi-tensor %s update)" % kind,
+                "traffic": traffic, "traffic_source": "profiles/traffic_r1.json (ncu --set full, one launch)",
+                "kernel": "mta_kernel (fused multi-tensor %s update)" % kind,
                 "algorithmic_bytes_per_step": alg, "bytes_per_element": bpe,
                 "kernel_ms_per_step": k_ms, "kernel_share_of_step": k_ms / ms_step,
                 "launches_per_step": launches / args.steps, "peak_source": peak_src,

@@ -232,6 +232,23 @@ int b200kv_multi_lamb_update(int num, int dtype, void* const* weights, const voi
 int b200kv_multi_sum_sq(int num, int dtype, const void* const* arrays, const int64_t* sizes,
                         float* out, void* stream);
 
+/* _multi_adamw_update / _multi_mp_adamw_update (src/operator/contrib/adamw-inl.h:326-460,
+ * adamw.cu:32-41): per-tensor lrs / wds / etas; `rescale_grad_dev` is a DEVICE pointer to the
+ * loss-scale reciprocal — a non-finite or zero value skips the whole update, decided on the GPU
+ * (the reference copies the scalar to the host and synchronises the stream).  No 50-tensor limit. */
+int b200kv_multi_adamw_update(int num, int dtype, void* const* weights, const void* const* grads,
+                              float* const* means, float* const* vars, float* const* weights32,
+                              const int64_t* sizes, const float* lrs, const float* wds, const float* etas,
+                              float beta1, float beta2, float epsilon, const float* rescale_grad_dev,
+                              float clip_gradient, void* stream);
+/* multi_all_finite (src/operator/contrib/all_finite.cc:64-95, all_finite.cu:33-93): out[0] (device
+ * float) becomes 0 if any element of any array is inf / nan; it is first set to 1 when init_output. */
+int b200kv_multi_all_finite(int num, int dtype, const void* const* arrays, const int64_t* sizes,
+                            int init_output, float* out, void* stream);
+/* reset_arrays (src/operator/contrib/reset_arrays.cc, .cu:33): zero all arrays in one launch
+ * (the reference issues one cudaMemsetAsync per array). */
+int b200kv_reset_arrays(int num, int dtype, void* const* arrays, const int64_t* sizes, void* stream);
+
 /* gluon.utils.clip_global_norm (python/mxnet/gluon/utils.py:122-161) as one fused sequence:
  * total = sqrt(sum_i sum(x_i^2)); scale = min(max_norm / (total + 1e-8), 1); every array *= scale
  * in place (rounded in the array dtype).  out_scale_norm: device pointer to two floats that

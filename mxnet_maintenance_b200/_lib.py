@@ -75,6 +75,10 @@ SIGNATURES = {
     "b200kv_multi_lamb_update": [_I, _I, _PVP, _PVP, _PVP, _PVP, _PVP, C.POINTER(_I64), _PF, _PF,
                                  _PI, _F, _F, _F, _F, _F, _F, _F, _I, _VP],
     "b200kv_multi_sum_sq": [_I, _I, _PVP, C.POINTER(_I64), _VP, _VP],
+    "b200kv_multi_adamw_update": [_I, _I, _PVP, _PVP, _PVP, _PVP, _PVP, C.POINTER(_I64), _PF, _PF, _PF,
+                                  _F, _F, _F, _VP, _F, _VP],
+    "b200kv_multi_all_finite": [_I, _I, _PVP, C.POINTER(_I64), _I, _VP, _VP],
+    "b200kv_reset_arrays": [_I, _I, _PVP, C.POINTER(_I64), _VP],
     "b200kv_clip_global_norm": [_I, _I, _PVP, C.POINTER(_I64), _F, _VP, _VP],
     "b200kv_multi_sum_sq_static": [_I, _I, _PVP, C.POINTER(_I64), _VP, _VP],
 }

@@ -422,6 +422,72 @@ int b200kv_multi_lamb_update(int num, int dtype, void* const* weights, const voi
   API_END();
 }
 
+int b200kv_multi_adamw_update(int num, int dtype, void* const* weights, const void* const* grads,
+                              float* const* means, float* const* vars, float* const* weights32,
+                              const int64_t* sizes, const float* lrs, const float* wds, const float* etas,
+                              float beta1, float beta2, float epsilon, const float* rescale_grad_dev,
+                              float clip_gradient, void* stream) {
+  API_BEGIN();
+  if (num <= 0) return 0;
+  KV_CHECK(rescale_grad_dev != nullptr, "rescale_grad must be a device pointer to one float");
+  const int dev = current_device();
+  OpWorkspace& w = workspace(dev);
+  std::lock_guard<std::mutex> lk(w.mu);
+  prepare_plan(w, num, sizes);
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  MtaCall c = make_call(w, num, dtype, weights, grads, means, vars, weights32, lrs, wds, etas, nullptr, st, dev);
+  OptScalars s;
+  s.beta1 = beta1; s.beta2 = beta2; s.eps = epsilon; s.clip = clip_gradient;
+  launch_adamw(c, s, rescale_grad_dev);
+  w.ring.end(st);
+  API_END();
+}
+
+int b200kv_multi_all_finite(int num, int dtype, const void* const* arrays, const int64_t* sizes,
+                            int init_output, float* out, void* stream) {
+  API_BEGIN();
+  if (num <= 0) return 0;
+  const int dev = current_device();
+  OpWorkspace& w = workspace(dev);
+  std::lock_guard<std::mutex> lk(w.mu);
+  prepare_plan(w, num, sizes);
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  KV_CHECK(dtype == kF32 || dtype == kF16, "dtype must be 0 (float32) or 2 (float16)");
+  Table t{w.ring.begin(mta_blob_words(num, 1, 0) * 8), num, 1, 0};
+  std::memset(t.p, 0, mta_blob_words(num, 1, 0) * 8);
+  for (int i = 0; i < num; ++i) t.G(0, i, arrays[i]);
+  MtaCall c;
+  c.blob = w.ring.commit(st);
+  c.plan = &w.plan;
+  c.nt = num; c.ngrad = 1; c.nout = 0; c.dtype = dtype; c.stream = st; c.device = dev;
+  launch_nonfinite(c, w.partials.as<float>());
+  launch_reduce_partials(w.partials.as<float>(), w.plan, 1, w.sums.as<float>(), st);
+  launch_all_finite_final(w.sums.as<float>(), num, init_output, out, st);
+  w.ring.end(st);
+  API_END();
+}
+
+int b200kv_reset_arrays(int num, int dtype, void* const* arrays, const int64_t* sizes, void* stream) {
+  API_BEGIN();
+  if (num <= 0) return 0;
+  const int dev = current_device();
+  OpWorkspace& w = workspace(dev);
+  std::lock_guard<std::mutex> lk(w.mu);
+  prepare_plan(w, num, sizes);
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  KV_CHECK(dtype == kF32 || dtype == kF16, "dtype must be 0 (float32) or 2 (float16)");
+  Table t{w.ring.begin(mta_blob_words(num, 1, 1) * 8), num, 1, 1};
+  std::memset(t.p, 0, mta_blob_words(num, 1, 1) * 8);
+  for (int i = 0; i < num; ++i) t.G(1, i, arrays[i]);   // the out section
+  MtaCall c;
+  c.blob = w.ring.commit(st);
+  c.plan = &w.plan;
+  c.nt = num; c.ngrad = 1; c.nout = 1; c.dtype = dtype; c.stream = st; c.device = dev;
+  launch_zero(c);
+  w.ring.end(st);
+  API_END();
+}
+
 int b200kv_clip_global_norm(int num, int dtype, void* const* arrays, const int64_t* sizes,
                             float max_norm, float* out_scale_norm, void* stream) {
   API_BEGIN();

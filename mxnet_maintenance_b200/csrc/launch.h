@@ -29,6 +29,12 @@ struct OptScalars {
 // Update kernels: W section is the fp32 weight (dtype kF32) or the fp32 master (dtype kF16).
 int launch_sgd(const MtaCall& c, bool has_mom, const OptScalars& s, const float* gscale);
 int launch_adam(const MtaCall& c, const OptScalars& s, const float* gscale);
+int launch_adamw(const MtaCall& c, const OptScalars& s, const float* rescale_dev);
+// partials [nchunks]: number of non-finite values per chunk
+int launch_nonfinite(const MtaCall& c, float* partials);
+int launch_all_finite_final(const float* sums, int nt, int init_output, float* out, cudaStream_t stream);
+// out copies <- 0
+int launch_zero(const MtaCall& c);
 // partials: [nchunks][2] floats
 int launch_lamb1(const MtaCall& c, const OptScalars& s, const float* gscale, float* partials);
 int launch_lamb2(const MtaCall& c, const OptScalars& s, const float* ratio);
@@ -42,13 +48,9 @@ int launch_scale(const MtaCall& c, const float* gscale);
 // out copies (dtype) <- W section (fp32 master)
 int launch_master_to_out(const MtaCall& c);
 
-// peer-memory barrier (see optim.cuh): which = 0 "gradients ready", 1 "weights written"
-struct P2PFlagsHost {
-  uint32_t* flags[kMaxCopies];
-  int world, rank;
-  uint32_t epoch;
-};
-int launch_p2p_barrier(const P2PFlagsHost& f, int which, cudaStream_t stream);
+// stand-alone peer-memory barrier kernel (see optim.cuh): which = 0 "gradients ready",
+// 1 "weights written"; used around the TMA-staged kernels, which carry no in-kernel barrier
+int launch_p2p_barrier(const P2PFlags& f, int which, cudaStream_t stream);
 
 // TMA-staged forms (staged.cu); -1 = not eligible, use the plain launcher
 int launch_sgd_staged(const MtaCall& c, bool has_mom, const OptScalars& s, const float* gscale);

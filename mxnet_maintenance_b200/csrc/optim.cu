@@ -87,6 +87,31 @@ int launch_adam(const MtaCall& c, const OptScalars& s, const float* gscale) {
   return launch_update(c, op, gscale, nullptr);
 }
 
+int launch_adamw(const MtaCall& c, const OptScalars& s, const float* rescale_dev) {
+  AdamWOp op{s.beta1, s.beta2, s.eps, s.clip, rescale_dev};
+  return launch_update(c, op, nullptr, nullptr);
+}
+
+int launch_nonfinite(const MtaCall& c, float* partials) {
+  NonFiniteOp op;
+  if (c.dtype == kF32) return launch_ng<NonFiniteOp, float, float>(c, op, nullptr, partials);
+  KV_CHECK(c.dtype == kF16, "unsupported dtype " << c.dtype);
+  return launch_ng<NonFiniteOp, __half, __half>(c, op, nullptr, partials);
+}
+
+int launch_all_finite_final(const float* sums, int nt, int init_output, float* out, cudaStream_t stream) {
+  all_finite_final_kernel<<<1, 256, 0, stream>>>(sums, nt, init_output, out);
+  CUDA_OK(cudaGetLastError());
+  return 1;
+}
+
+int launch_zero(const MtaCall& c) {
+  ZeroOp op;
+  if (c.dtype == kF32) return launch_ng<ZeroOp, float, float>(c, op, nullptr, nullptr);
+  KV_CHECK(c.dtype == kF16, "unsupported dtype " << c.dtype);
+  return launch_ng<ZeroOp, __half, __half>(c, op, nullptr, nullptr);
+}
+
 int launch_lamb1(const MtaCall& c, const OptScalars& s, const float* gscale, float* partials) {
   Lamb1Op op{s.beta1, s.beta2, s.eps, s.rescale, s.clip, s.bias_correction};
   return launch_update(c, op, gscale, partials);
@@ -137,12 +162,7 @@ int launch_master_to_out(const MtaCall& c) {
   return launch_ng<MasterToOutOp, __half, float>(c, op, nullptr, nullptr);
 }
 
-int launch_p2p_barrier(const P2PFlagsHost& h, int which, cudaStream_t stream) {
-  P2PFlags f;
-  for (int k = 0; k < kMaxCopies; ++k) f.flags[k] = h.flags[k];
-  f.world = h.world;
-  f.rank = h.rank;
-  f.epoch = h.epoch;
+int launch_p2p_barrier(const P2PFlags& f, int which, cudaStream_t stream) {
   p2p_barrier_kernel<<<1, 32, 0, stream>>>(f, which);
   CUDA_OK(cudaGetLastError());
   return 1;

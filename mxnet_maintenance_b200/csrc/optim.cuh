@@ -188,6 +188,71 @@ struct AdamOp {
   }
 };
 
+// _multi_adamw_update / _multi_mp_adamw_update: MultiMPAdamWKernel::Map
+// (src/operator/contrib/adamw-inl.h:346-377).  aux0 = eta.  rescale_grad is a DEVICE scalar; a
+// non-finite or zero value skips the update (MPUpdate, adamw-inl.h:447-460) — decided on the
+// device, where the reference copies the scalar to the host and synchronises (adamw.cu:32-41).
+struct AdamWOp {
+  static constexpr OpFlags F = {true, true, true, true, true, true, true, true, 0};
+  float beta1, beta2, eps, clip;
+  const float* rescale;
+  struct PT { float lr, wd, eta, rs; bool skip; };
+  __device__ __forceinline__ PT prep(float lr, float wd, float a0, float) const {
+    const float rs = *rescale;
+    return {lr, wd, a0, rs, !isfinite(rs) || rs == 0.f};
+  }
+  template <typename T>
+  __device__ __forceinline__ void elem(const PT& p, float& w, float g, float& m, float& v,
+                                       float*) const {
+    if (p.skip) return;
+    float sg = __fmul_rn(p.rs, g);
+    if (clip >= 0.0f) sg = clipf(sg, clip);
+    const float mean = __fadd_rn(__fmul_rn(beta1, __fsub_rn(m, sg)), sg);
+    const float adj = __fmul_rn(sg, sg);
+    const float var = __fadd_rn(__fmul_rn(beta2, __fsub_rn(v, adj)), adj);
+    m = mean;
+    v = var;
+    const float upd = __fadd_rn(__fdiv_rn(__fmul_rn(p.lr, mean), __fadd_rn(__fsqrt_rn(var), eps)),
+                                __fmul_rn(p.wd, w));
+    w = __fsub_rn(w, __fmul_rn(p.eta, upd));
+  }
+};
+
+// multi_all_finite (src/operator/contrib/all_finite.cc:64-95): counts non-finite values
+struct NonFiniteOp {
+  static constexpr OpFlags F = {true, false, false, false, false, false, false, false, 1};
+  struct PT {};
+  __device__ __forceinline__ PT prep(float, float, float, float) const { return {}; }
+  template <typename T>
+  __device__ __forceinline__ void elem(const PT&, float&, float g, float&, float&, float* red) const {
+    if (!isfinite(g)) red[0] = __fadd_rn(red[0], 1.0f);
+  }
+};
+
+// reset_arrays (src/operator/contrib/reset_arrays.cc): zero every array (the out copies)
+struct ZeroOp {
+  static constexpr OpFlags F = {false, false, false, true, false, false, false, false, 0};
+  struct PT {};
+  __device__ __forceinline__ PT prep(float, float, float, float) const { return {}; }
+  template <typename T>
+  __device__ __forceinline__ void elem(const PT&, float& w, float, float&, float&, float*) const { w = 0.f; }
+};
+
+// out[0] = 0 when any count is positive; = 1 first when init_output (all_finite.cc:84-86)
+static __global__ void all_finite_final_kernel(const float* __restrict__ sums, int nt, int init_output,
+                                               float* __restrict__ out) {
+  __shared__ int bad;
+  if (threadIdx.x == 0) bad = 0;
+  __syncthreads();
+  for (int t = threadIdx.x; t < nt; t += blockDim.x)
+    if (sums[t] > 0.f) bad = 1;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    if (bad) out[0] = 0.f;
+    else if (init_output) out[0] = 1.f;
+  }
+}
+
 // LAMB update direction u = m_hat/(sqrt(v_hat)+eps) + wd*w   (multi_lamb.cc:56-72)
 // aux0 = 1 - beta1^t, aux1 = 1 - beta2^t (computed with the host's powf, as the CPU kernel does)
 __device__ __forceinline__ float lamb_dir(float m, float v, float w, float wd, float c1, float c2,

@@ -60,6 +60,20 @@ Store::Store(int device, int rank, int world) : device_(device), rank_(rank), wo
 Store::~Store() {
   cudaSetDevice(device_);
   cudaStreamSynchronize(stream_);
+  for (auto& sp : segs_) {   // unmap the peers' buffers before our own are freed
+    Segment::P2P& P = sp->p2p;
+    if (!P.ok) continue;
+    for (int k = 0; k < world_; ++k) {
+      if (k == rank_) continue;
+      if (P.g[k]) cudaIpcCloseMemHandle(P.g[k]);
+      if (P.w[k]) cudaIpcCloseMemHandle(P.w[k]);
+      if (P.flags[k]) cudaIpcCloseMemHandle(P.flags[k]);
+    }
+  }
+  for (auto& e : prof_events_) {
+    cudaEventDestroy(e.first);
+    cudaEventDestroy(e.second);
+  }
   if (comm_) NcclApi::get().CommDestroy(reinterpret_cast<ncclComm_t>(comm_));
 }
 
@@ -68,6 +82,14 @@ void Store::use_device() { CUDA_OK(cudaSetDevice(device_)); }
 void Store::wait() {
   use_device();
   CUDA_OK(cudaStreamSynchronize(stream_));
+  // a peer that never arrived at a cross-GPU barrier leaves an error flag instead of a hung GPU
+  for (auto& sp : segs_) {
+    if (!sp->p2p.ok) continue;
+    uint32_t err = 0;
+    CUDA_OK(cudaMemcpy(&err, sp->p2p.local_flags.as<uint32_t>() + 16, sizeof(err), cudaMemcpyDeviceToHost));
+    KV_CHECK(err == 0, "a peer GPU did not reach the gradient-exchange barrier within the time limit; "
+                       "the weights of the last step are not valid");
+  }
 }
 
 void Store::comm_init(const char id[128]) {
@@ -86,8 +108,12 @@ void Store::barrier() {
   use_device();
   if (world_ > 1) {
     KV_CHECK(comm_, "b200kv_comm_init has not been called");
-    NCCL_OK(NcclApi::get().AllReduce(gnorm_.p, gnorm_.p, 0, ncclFloat32, ncclSum,
+    DevBuf tmp;
+    tmp.reserve(16);
+    CUDA_OK(cudaMemsetAsync(tmp.p, 0, 16, stream_));
+    NCCL_OK(NcclApi::get().AllReduce(tmp.p, tmp.p, 1, ncclFloat32, ncclSum,
                                      reinterpret_cast<ncclComm_t>(comm_), stream_));
+    CUDA_OK(cudaStreamSynchronize(stream_));
   }
   CUDA_OK(cudaStreamSynchronize(stream_));
 }
@@ -723,7 +749,7 @@ void Store::run_class_p2p(DensePlan& p, Segment& s, const std::vector<const Entr
     prof_end();
   }
 
-  P2PFlagsHost f;
+  P2PFlags f;
   for (int k = 0; k < kMaxCopies; ++k) f.flags[k] = P.flags[k];
   f.world = W; f.rank = rank_; f.epoch = ++P.epoch;
   // Barriers: folded into the first peer-reading / last peer-writing kernel (plain kernels), or

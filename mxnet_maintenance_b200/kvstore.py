@@ -15,7 +15,6 @@ after ``pushpull`` every ``out`` holds the updated weight).
 """
 import ctypes as C
 import os
-import pickle
 
 from . import _lib
 from ._lib import B200KVError, OptimizerDesc, check_call
@@ -262,7 +261,7 @@ class B200(KVStoreBase):
             check_call(self._lib.b200kv_set_optimizer(self._h, C.byref(d)))
             self._opt_sent = desc
 
-    def _before_update(self, ckeys, keys):
+    def _before_update(self, keys):
         """Ship this step's scalars: the Python side of the updater callback (kvstore.py:34-41,
         optimizer.py:2078-2127) without any tensor work."""
         self._send_optimizer()
@@ -300,7 +299,7 @@ class B200(KVStoreBase):
             return self._push_rsp(keys, vals, use_str, priority)
         ck = self._keys(keys, use_str)
         self._bind_stream()
-        self._before_update(ck, keys)
+        self._before_update(keys)
         ptrs, keep = self._handles(vals, False)
         check_call(self._lib.b200kv_push(self._h, len(keys), ck, ptrs, priority))
 
@@ -331,7 +330,7 @@ class B200(KVStoreBase):
         cv = self._keys(vkeys, use_str)
         co = cv if okeys is vkeys else self._keys(okeys, use_str)
         self._bind_stream()
-        self._before_update(cv, vkeys)
+        self._before_update(vkeys)
         pv, keep_v = self._handles(vals, False)
         po, keep_o = (pv, keep_v) if outs is vals else self._handles(outs, True)
         check_call(self._lib.b200kv_pushpull(self._h, len(vkeys), cv, pv, len(okeys), co, po, priority))
@@ -349,7 +348,7 @@ class B200(KVStoreBase):
         cv = self._keys(vkeys, use_str)
         co = cv if okeys is vkeys else self._keys(okeys, use_str)
         self._bind_stream()
-        self._before_update(cv, vkeys)   # the first replay is a normal step
+        self._before_update(vkeys)   # the first replay is a normal step
         pv, keep_v = self._handles(vals, False)
         po, keep_o = (pv, keep_v) if outs is vals else self._handles(outs, True)
         bid = C.c_int()

@@ -108,6 +108,46 @@ def multi_sum_sq(arrays):
     return out
 
 
+def multi_adamw_update(weights, grads, means, vars_, rescale_grad, lrs, wds, etas, weights32=None,
+                       beta1=0.9, beta2=0.999, epsilon=1e-8, clip_gradient=-1.0):
+    """_multi_(mp_)adamw_update (python/mxnet/ndarray/contrib.py multi_adamw_update;
+    src/operator/contrib/adamw-inl.h:326-460).  `rescale_grad` is a 1-element float32 CUDA tensor;
+    a non-finite or zero value skips the update without any host synchronisation."""
+    lib = _lib.load()
+    n, sizes, stream = _common(weights, grads)
+    assert rescale_grad.is_cuda and rescale_grad.dtype == torch.float32 and rescale_grad.numel() == 1
+    with torch.cuda.device(weights[0].device):
+        check_call(lib.b200kv_multi_adamw_update(
+            n, _dtype_flag(weights[0]), _pp(weights), _pp(grads), _pp(means), _pp(vars_),
+            _pp(weights32) if weights32 is not None else None, sizes, _f(lrs, n), _f(wds, n), _f(etas, n),
+            beta1, beta2, epsilon, C.c_void_p(rescale_grad.data_ptr()),
+            clip_gradient if clip_gradient is not None else -1.0, stream))
+
+
+def multi_all_finite(arrays, out=None, init_output=True):
+    """multi_all_finite: 1-element float32 CUDA tensor, 1.0 iff every value of every array is finite."""
+    lib = _lib.load()
+    n = len(arrays)
+    if out is None:
+        out = torch.empty(1, dtype=torch.float32, device=arrays[0].device)
+    sizes = (C.c_int64 * n)(*[a.numel() for a in arrays])
+    stream = C.c_void_p(torch.cuda.current_stream(arrays[0].device).cuda_stream)
+    with torch.cuda.device(arrays[0].device):
+        check_call(lib.b200kv_multi_all_finite(n, _dtype_flag(arrays[0]), _pp(arrays), sizes,
+                                               int(bool(init_output)), C.c_void_p(out.data_ptr()), stream))
+    return out
+
+
+def reset_arrays(arrays):
+    """reset_arrays: zero every array with one launch (fused zero-grad)."""
+    lib = _lib.load()
+    n = len(arrays)
+    sizes = (C.c_int64 * n)(*[a.numel() for a in arrays])
+    stream = C.c_void_p(torch.cuda.current_stream(arrays[0].device).cuda_stream)
+    with torch.cuda.device(arrays[0].device):
+        check_call(lib.b200kv_reset_arrays(n, _dtype_flag(arrays[0]), _pp(arrays), sizes, stream))
+
+
 def clip_global_norm(arrays, max_norm):
     """gluon.utils.clip_global_norm (python/mxnet/gluon/utils.py:122-161): rescales `arrays` in
     place so that their global 2-norm is at most `max_norm`.  Returns a 2-element CUDA tensor

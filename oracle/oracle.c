@@ -173,6 +173,38 @@ int mxref_adam(int64_t n, float* out, float* mean, float* var, const float* w, c
   return 0;
 }
 
+/* _multi_adamw_update / _multi_mp_adamw_update: MultiMPAdamWKernel::Map,
+ * src/operator/contrib/adamw-inl.h:346-377.
+ *   sg = rescale*g; clip; mean = b1*(m - sg) + sg; adj = sg*sg; var = b2*(v - adj) + adj;
+ *   w = w - eta*(lr*mean/(sqrt(var)+eps) + wd*w)
+ * A non-finite or zero rescale_grad skips the update (MPUpdate, adamw-inl.h:447-460). */
+int mxref_multi_adamw(int dtype, int has_mp, int count, void** weights, void** grads, void** means,
+                      void** vars, void** w32, void** outs, const int64_t* sizes, const float* lrs,
+                      const float* wds, const float* etas, float beta1, float beta2, float eps,
+                      float rescale, float clip, int nthread) {
+  if (!((dtype == 0 && !has_mp) || (dtype == 2 && has_mp))) return -1;
+  if (!isfinite(rescale) || rescale == 0) return 0;
+  for (int t = 0; t < count; ++t) {
+    const int64_t n = sizes[t];
+    float* mean = (float*)means[t]; float* var = (float*)vars[t];
+    const float lr = lrs[t], wd = wds[t], eta = etas[t];
+#pragma omp parallel for num_threads(nthread)
+    for (int64_t i = 0; i < n; ++i) {
+      float w = has_mp ? ((float*)w32[t])[i] : ((const float*)weights[t])[i];
+      float sg = rescale * (dtype == 0 ? ((const float*)grads[t])[i] : h2f(((const f16*)grads[t])[i]));
+      if (clip >= 0.0f) sg = clipf(sg, clip);
+      const float m = beta1 * (mean[i] - sg) + sg;
+      const float adj = sg * sg;
+      const float v = beta2 * (var[i] - adj) + adj;
+      mean[i] = m; var[i] = v;
+      w = w - eta * (lr * m / (sqrtf(v) + eps) + wd * w);
+      if (has_mp) { ((float*)w32[t])[i] = w; ((f16*)outs[t])[i] = f2h(w); }
+      else ((float*)outs[t])[i] = w;
+    }
+  }
+  return 0;
+}
+
 /* ------------------------------------------------------------------------------------------
  * multi_sum_sq CPU: CalcSumSq, src/operator/contrib/multi_sum_sq.cc:68-84 — one thread per array,
  * strictly sequential fp32 accumulation inside an array.

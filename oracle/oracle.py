@@ -86,6 +86,7 @@ class Oracle:
         L.mxref_adam.argtypes = [C.c_int64] + [C.c_void_p] * 5 + [fp] * 7 + [C.c_int]
         L.mxref_multi_lamb.argtypes = ([C.c_int] * 3 + [C.c_void_p] * 10 + [fp] * 7 + [C.c_int] * 2
                                        + [C.c_void_p] * 2)
+        L.mxref_multi_adamw.argtypes = ([C.c_int] * 3 + [C.c_void_p] * 10 + [fp] * 5 + [C.c_int])
         L.mxref_multi_sum_sq.argtypes = [C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int]
         L.mxref_sgd_mom_rsp.argtypes = [C.c_int64, C.c_int64] + [C.c_void_p] * 5 + [fp] * 5 + [C.c_int]
         L.mxref_adam_rsp.argtypes = [C.c_int64, C.c_int64] + [C.c_void_p] * 6 + [fp] * 7 + [C.c_int]
@@ -168,6 +169,19 @@ class Oracle:
                                        self.nthread, r1.ctypes.data, r2.ctypes.data)
         assert rc == 0
         return r1, r2
+
+    def multi_adamw(self, weights, grads, means, vars_, w32s, lrs, wds, etas, beta1=0.9, beta2=0.999,
+                    eps=1e-8, rescale=1.0, clip=-1.0):
+        """_multi_(mp_)adamw_update in place (contrib/adamw-inl.h:326-460)."""
+        has_mp = w32s is not None
+        n = len(weights)
+        sizes = _i64([w.size for w in weights])
+        lrs, wds, etas = _f32(lrs), _f32(wds), _f32(etas)
+        rc = self.lib.mxref_multi_adamw(_flag(weights[0]), int(has_mp), n, _pp(weights), _pp(grads),
+                                        _pp(means), _pp(vars_), _pp(w32s) if has_mp else None,
+                                        _pp(weights), sizes.ctypes.data, lrs.ctypes.data, wds.ctypes.data,
+                                        etas.ctypes.data, beta1, beta2, eps, rescale, clip, self.nthread)
+        assert rc == 0
 
     def multi_sum_sq(self, arrays):
         out = np.zeros(len(arrays), np.float32)

@@ -15,6 +15,7 @@
 //   MultiLAMBKernelStep1/2    src/operator/contrib/multi_lamb.cc:33-118
 //   CalcSumSq                 src/operator/contrib/multi_sum_sq.cc:68-84
 //   SparseRetainRspThreadKernel src/operator/tensor/sparse_retain-inl.h:121-150
+//   MultiMPAdamWKernel        src/operator/contrib/adamw-inl.h:346-377
 //   mshadow half_t / Tensor<cpu,1,DType> expressions for the CommCPU reduce
 //                             (restated driver: src/kvstore/comm.h:357-410)
 #include <cstdint>
@@ -25,6 +26,7 @@
 
 #include "operator/optimizer_op-inl.h"
 #include "operator/tensor/sparse_retain-inl.h"
+#include "operator/contrib/adamw-inl.h"
 // The LAMB step functors and CalcSumSq live in .cc files; pull them in as-is.
 #include "operator/contrib/multi_sum_sq.cc"
 #include "operator/contrib/multi_lamb.cc"
@@ -181,6 +183,35 @@ void RunMultiLAMB(int count, void** weights, void** grads, void** means, void** 
   }
 }
 
+// _multi_adamw_update / _multi_mp_adamw_update (contrib/adamw-inl.h:326-377; N = 50 tensors per launch)
+template <typename DType, typename MPDType, bool has_mp>
+static void RunMultiAdamW(int count, void** weights, void** grads, void** means, void** vars, void** w32,
+                          void** outs, const int64_t* sizes, const float* lrs, const float* wds,
+                          const float* etas, float beta1, float beta2, float eps, float rescale,
+                          float clip, int nthread) {
+  using KP = MultiAdamKernelParam<DType, MPDType>;
+  for (int base = 0; base < count; base += KP::N) {
+    KP p;
+    p.count = std::min(count - base, static_cast<int>(KP::N));
+    p.max_size = 0;
+    p.clip_gradient = clip; p.beta1 = beta1; p.beta2 = beta2; p.epsilon = eps;
+    for (int i = 0; i < p.count; ++i) {
+      p.sizes[i] = sizes[base + i];
+      p.max_size = std::max(p.max_size, p.sizes[i]);
+      p.weights[i] = static_cast<DType*>(weights[base + i]);
+      p.grad_data[i] = static_cast<DType*>(grads[base + i]);
+      p.mean_data[i] = static_cast<MPDType*>(means[base + i]);
+      p.var_data[i] = static_cast<MPDType*>(vars[base + i]);
+      p.weights32[i] = has_mp ? static_cast<MPDType*>(w32[base + i]) : nullptr;
+      p.out_data[i] = static_cast<DType*>(outs[base + i]);
+      p.etas[i] = etas[base + i]; p.lrs[i] = lrs[base + i]; p.wds[i] = wds[base + i];
+    }
+    const int N = static_cast<int>(p.max_size);
+#pragma omp parallel for num_threads(nthread)
+    for (int i = 0; i < N; ++i) MultiMPAdamWKernel<MPDType, has_mp>::Map(i, p, kWriteTo, rescale);
+  }
+}
+
 }  // namespace
 
 extern "C" {
@@ -260,6 +291,23 @@ int mxref_multi_lamb(int dtype, int has_mp, int count, void** weights, void** gr
     RunMultiLAMB<half_t, float, true>(count, weights, grads, means, vars, w32, outs, sizes, lrs, wds,
                                       steps, beta1, beta2, eps, rescale, clip, lower, upper,
                                       bias_correction, nthread, r1_out, r2_out);
+  else
+    return -1;
+  return 0;
+}
+
+int mxref_multi_adamw(int dtype, int has_mp, int count, void** weights, void** grads, void** means,
+                      void** vars, void** w32, void** outs, const int64_t* sizes, const float* lrs,
+                      const float* wds, const float* etas, float beta1, float beta2, float eps,
+                      float rescale, float clip, int nthread) {
+  // MPUpdate (adamw-inl.h:447-460): a non-finite or zero rescale_grad skips the whole update
+  if (!std::isfinite(rescale) || rescale == 0) return 0;
+  if (dtype == 0 && !has_mp)
+    RunMultiAdamW<float, float, false>(count, weights, grads, means, vars, w32, outs, sizes, lrs, wds, etas,
+                                       beta1, beta2, eps, rescale, clip, nthread);
+  else if (dtype == 2 && has_mp)
+    RunMultiAdamW<half_t, float, true>(count, weights, grads, means, vars, w32, outs, sizes, lrs, wds, etas,
+                                       beta1, beta2, eps, rescale, clip, nthread);
   else
     return -1;
   return 0;

@@ -133,3 +133,25 @@ def test_row_sparse_kernels(oracle, oracle_ref):
     ra = oracle.sparse_retain(idx, gg, [0, 1, 7, 29, 30, 49])
     rb = oracle_ref.sparse_retain(idx, gg, [0, 1, 7, 29, 30, 49])
     assert ra[0].tobytes() == rb[0].tobytes() and ra[1].tobytes() == rb[1].tobytes()
+
+
+@pytest.mark.parametrize("mp", [False, True])
+@pytest.mark.parametrize("clip", [-1.0, 0.004])
+def test_multi_adamw(oracle, oracle_ref, mp, clip):
+    rng = np.random.default_rng(8)
+    sizes = [3, 1000, 40001]
+    dt = np.float16 if mp else np.float32
+    w = [rng.uniform(-1, 1, s).astype(np.float32).astype(dt) for s in sizes]
+    g = [(rng.uniform(-1, 1, s) * 1e-2).astype(np.float32).astype(dt) for s in sizes]
+
+    def f(o):
+        ww = [x.copy() for x in w]
+        me = [np.zeros(s, np.float32) for s in sizes]
+        va = [np.zeros(s, np.float32) for s in sizes]
+        w32 = [x.astype(np.float32) for x in ww] if mp else None
+        for t in range(4):
+            o.multi_adamw(ww, g, me, va, w32, [1e-3, 2e-3, 5e-4], [0.01, 0, 0.1], [1.0, 0.5, 2.0],
+                          rescale=[0.5, 0.25, float("nan"), 0.5][t], clip=clip)
+        return np.concatenate([x.astype(np.float32) for x in ww] + me + va)
+    a, b = _both(oracle, oracle_ref, f)
+    assert a.tobytes() == b.tobytes()

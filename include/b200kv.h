@@ -232,6 +232,19 @@ int b200kv_multi_lamb_update(int num, int dtype, void* const* weights, const voi
 int b200kv_multi_sum_sq(int num, int dtype, const void* const* arrays, const int64_t* sizes,
                         float* out, void* stream);
 
+/* multi_lars (src/operator/contrib/multi_lars-inl.h:60-98): layer-wise learning rates from the
+ * per-tensor sums of squares that b200kv_multi_sum_sq produces.  All arrays are DEVICE arrays of
+ * `num` floats. */
+int b200kv_multi_lars(int num, const float* lrs, const float* weights_sum_sq, const float* grads_sum_sq,
+                      const float* wds, float eta, float eps, float rescale_grad, float* out_lrs,
+                      void* stream);
+/* preloaded_multi_sgd_update / preloaded_multi_sgd_mom_update / preloaded_multi_mp_sgd(_mom)_update
+ * (src/operator/contrib/preloaded_multi_sgd-inl.h:160-260): as b200kv_multi_sgd_update, with the
+ * learning rates and weight decays read from DEVICE arrays (the outputs of multi_lars). */
+int b200kv_preloaded_multi_sgd_update(int num, int dtype, void* const* weights, const void* const* grads,
+                                      float* const* moms, float* const* weights32, const int64_t* sizes,
+                                      const float* lrs_dev, const float* wds_dev, float momentum,
+                                      float rescale_grad, float clip_gradient, void* stream);
 /* _multi_adamw_update / _multi_mp_adamw_update (src/operator/contrib/adamw-inl.h:326-460,
  * adamw.cu:32-41): per-tensor lrs / wds / etas; `rescale_grad_dev` is a DEVICE pointer to the
  * loss-scale reciprocal — a non-finite or zero value skips the whole update, decided on the GPU

@@ -75,6 +75,9 @@ SIGNATURES = {
     "b200kv_multi_lamb_update": [_I, _I, _PVP, _PVP, _PVP, _PVP, _PVP, C.POINTER(_I64), _PF, _PF,
                                  _PI, _F, _F, _F, _F, _F, _F, _F, _I, _VP],
     "b200kv_multi_sum_sq": [_I, _I, _PVP, C.POINTER(_I64), _VP, _VP],
+    "b200kv_multi_lars": [_I, _VP, _VP, _VP, _VP, _F, _F, _F, _VP, _VP],
+    "b200kv_preloaded_multi_sgd_update": [_I, _I, _PVP, _PVP, _PVP, _PVP, C.POINTER(_I64), _VP, _VP, _F, _F,
+                                          _F, _VP],
     "b200kv_multi_adamw_update": [_I, _I, _PVP, _PVP, _PVP, _PVP, _PVP, C.POINTER(_I64), _PF, _PF, _PF,
                                   _F, _F, _F, _VP, _F, _VP],
     "b200kv_multi_all_finite": [_I, _I, _PVP, C.POINTER(_I64), _I, _VP, _VP],

@@ -422,6 +422,37 @@ int b200kv_multi_lamb_update(int num, int dtype, void* const* weights, const voi
   API_END();
 }
 
+int b200kv_multi_lars(int num, const float* lrs, const float* weights_sum_sq, const float* grads_sum_sq,
+                      const float* wds, float eta, float eps, float rescale_grad, float* out_lrs,
+                      void* stream) {
+  API_BEGIN();
+  launch_multi_lars(num, lrs, weights_sum_sq, grads_sum_sq, wds, eta, eps, rescale_grad, out_lrs,
+                    static_cast<cudaStream_t>(stream));
+  API_END();
+}
+
+int b200kv_preloaded_multi_sgd_update(int num, int dtype, void* const* weights, const void* const* grads,
+                                      float* const* moms, float* const* weights32, const int64_t* sizes,
+                                      const float* lrs_dev, const float* wds_dev, float momentum,
+                                      float rescale_grad, float clip_gradient, void* stream) {
+  API_BEGIN();
+  if (num <= 0) return 0;
+  KV_CHECK(lrs_dev != nullptr && wds_dev != nullptr, "lrs / wds must be device arrays of `num` floats");
+  const int dev = current_device();
+  OpWorkspace& w = workspace(dev);
+  std::lock_guard<std::mutex> lk(w.mu);
+  prepare_plan(w, num, sizes);
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  MtaCall c = make_call(w, num, dtype, weights, grads, moms, nullptr, weights32, nullptr, nullptr, nullptr,
+                        nullptr, st, dev);
+  launch_fill_lrwd(c, lrs_dev, wds_dev);
+  OptScalars s;
+  s.momentum = momentum; s.rescale = rescale_grad; s.clip = clip_gradient;
+  launch_sgd(c, moms != nullptr, s, nullptr);
+  w.ring.end(st);
+  API_END();
+}
+
 int b200kv_multi_adamw_update(int num, int dtype, void* const* weights, const void* const* grads,
                               float* const* means, float* const* vars, float* const* weights32,
                               const int64_t* sizes, const float* lrs, const float* wds, const float* etas,

@@ -35,6 +35,10 @@ int launch_nonfinite(const MtaCall& c, float* partials);
 int launch_all_finite_final(const float* sums, int nt, int init_output, float* out, cudaStream_t stream);
 // out copies <- 0
 int launch_zero(const MtaCall& c);
+int launch_multi_lars(int n, const float* lrs, const float* w2, const float* g2, const float* wds, float eta,
+                      float eps, float rescale, float* out, cudaStream_t stream);
+// overwrite the (lr, wd) section of an uploaded table from device arrays
+int launch_fill_lrwd(const MtaCall& c, const float* lrs_dev, const float* wds_dev);
 // partials: [nchunks][2] floats
 int launch_lamb1(const MtaCall& c, const OptScalars& s, const float* gscale, float* partials);
 int launch_lamb2(const MtaCall& c, const OptScalars& s, const float* ratio);

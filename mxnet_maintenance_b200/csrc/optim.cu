@@ -112,6 +112,21 @@ int launch_zero(const MtaCall& c) {
   return launch_ng<ZeroOp, __half, __half>(c, op, nullptr, nullptr);
 }
 
+int launch_multi_lars(int n, const float* lrs, const float* w2, const float* g2, const float* wds, float eta,
+                      float eps, float rescale, float* out, cudaStream_t stream) {
+  if (n <= 0) return 0;
+  multi_lars_kernel<<<(n + 255) / 256, 256, 0, stream>>>(n, lrs, w2, g2, wds, eta, eps, rescale, out);
+  CUDA_OK(cudaGetLastError());
+  return 1;
+}
+
+int launch_fill_lrwd(const MtaCall& c, const float* lrs_dev, const float* wds_dev) {
+  uint64_t* section = const_cast<uint64_t*>(c.blob) + static_cast<size_t>(c.ngrad + c.nout + kSecLrWd) * c.nt;
+  fill_lrwd_kernel<<<(c.nt + 255) / 256, 256, 0, c.stream>>>(section, lrs_dev, wds_dev, c.nt);
+  CUDA_OK(cudaGetLastError());
+  return 1;
+}
+
 int launch_lamb1(const MtaCall& c, const OptScalars& s, const float* gscale, float* partials) {
   Lamb1Op op{s.beta1, s.beta2, s.eps, s.rescale, s.clip, s.bias_correction};
   return launch_update(c, op, gscale, partials);

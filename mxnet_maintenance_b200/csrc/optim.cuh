@@ -238,6 +238,27 @@ struct ZeroOp {
   __device__ __forceinline__ void elem(const PT&, float& w, float, float&, float&, float*) const { w = 0.f; }
 };
 
+// multi_lars: MultiLARSKernel::Map (src/operator/contrib/multi_lars-inl.h:60-72)
+static __global__ void multi_lars_kernel(int n, const float* __restrict__ lrs, const float* __restrict__ w2,
+                                         const float* __restrict__ g2, const float* __restrict__ wds,
+                                         float eta, float eps, float rescale, float* __restrict__ out) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const float w_norm = __fsqrt_rn(w2[i]);
+  const bool valid = w_norm > 0.f && g2[i] > 0.f;
+  const float num = __fmul_rn(__fmul_rn(lrs[i], eta), w_norm);
+  const float den = __fadd_rn(__fadd_rn(__fmul_rn(__fsqrt_rn(g2[i]), rescale), __fmul_rn(wds[i], w_norm)), eps);
+  out[i] = valid ? __fdiv_rn(num, den) : lrs[i];
+}
+
+// preloaded_multi_*sgd*: learning rates / weight decays come from device arrays
+// (src/operator/contrib/preloaded_multi_sgd-inl.h:160-195): patch the table's (lr, wd) section
+static __global__ void fill_lrwd_kernel(uint64_t* __restrict__ section, const float* __restrict__ lrs,
+                                        const float* __restrict__ wds, int nt) {
+  const int t = blockIdx.x * blockDim.x + threadIdx.x;
+  if (t < nt) reinterpret_cast<float2*>(section)[t] = make_float2(lrs[t], wds[t]);
+}
+
 // out[0] = 0 when any count is positive; = 1 first when init_output (all_finite.cc:84-86)
 static __global__ void all_finite_final_kernel(const float* __restrict__ sums, int nt, int init_output,
                                                float* __restrict__ out) {

@@ -108,6 +108,33 @@ def multi_sum_sq(arrays):
     return out
 
 
+def multi_lars(lrs, weights_sum_sq, grads_sum_sq, wds, eta, eps, rescale_grad=1.0):
+    """multi_lars: float32 CUDA tensors of one value per layer in, the adapted learning rates out."""
+    lib = _lib.load()
+    out = torch.empty_like(lrs)
+    stream = C.c_void_p(torch.cuda.current_stream(lrs.device).cuda_stream)
+    with torch.cuda.device(lrs.device):
+        check_call(lib.b200kv_multi_lars(lrs.numel(), C.c_void_p(lrs.data_ptr()),
+                                         C.c_void_p(weights_sum_sq.data_ptr()), C.c_void_p(grads_sum_sq.data_ptr()),
+                                         C.c_void_p(wds.data_ptr()), eta, eps, rescale_grad,
+                                         C.c_void_p(out.data_ptr()), stream))
+    return out
+
+
+def preloaded_multi_sgd_update(weights, grads, lrs, wds, moms=None, weights32=None, momentum=0.0,
+                               rescale_grad=1.0, clip_gradient=-1.0):
+    """preloaded_multi_(mp_)sgd(_mom)_update: `lrs` / `wds` are float32 CUDA tensors (one per array)."""
+    lib = _lib.load()
+    n, sizes, stream = _common(weights, grads)
+    assert lrs.is_cuda and wds.is_cuda and lrs.numel() == n and wds.numel() == n
+    with torch.cuda.device(weights[0].device):
+        check_call(lib.b200kv_preloaded_multi_sgd_update(
+            n, _dtype_flag(weights[0]), _pp(weights), _pp(grads), _pp(moms) if moms is not None else None,
+            _pp(weights32) if weights32 is not None else None, sizes, C.c_void_p(lrs.data_ptr()),
+            C.c_void_p(wds.data_ptr()), momentum, rescale_grad,
+            clip_gradient if clip_gradient is not None else -1.0, stream))
+
+
 def multi_adamw_update(weights, grads, means, vars_, rescale_grad, lrs, wds, etas, weights32=None,
                        beta1=0.9, beta2=0.999, epsilon=1e-8, clip_gradient=-1.0):
     """_multi_(mp_)adamw_update (python/mxnet/ndarray/contrib.py multi_adamw_update;

@@ -205,6 +205,17 @@ int mxref_multi_adamw(int dtype, int has_mp, int count, void** weights, void** g
   return 0;
 }
 
+/* multi_lars: MultiLARSKernel::Map, src/operator/contrib/multi_lars-inl.h:60-72 */
+int mxref_multi_lars(int n, float* out, const float* lrs, const float* w2, const float* g2,
+                     const float* wds, float eta, float eps, float rescale) {
+  for (int i = 0; i < n; ++i) {
+    float w_norm = sqrtf(w2[i]);
+    int valid = w_norm > 0. && g2[i] > 0.;
+    out[i] = valid ? lrs[i] * eta * w_norm / (sqrtf(g2[i]) * rescale + wds[i] * w_norm + eps) : lrs[i];
+  }
+  return 0;
+}
+
 /* ------------------------------------------------------------------------------------------
  * multi_sum_sq CPU: CalcSumSq, src/operator/contrib/multi_sum_sq.cc:68-84 — one thread per array,
  * strictly sequential fp32 accumulation inside an array.

@@ -87,6 +87,7 @@ class Oracle:
         L.mxref_multi_lamb.argtypes = ([C.c_int] * 3 + [C.c_void_p] * 10 + [fp] * 7 + [C.c_int] * 2
                                        + [C.c_void_p] * 2)
         L.mxref_multi_adamw.argtypes = ([C.c_int] * 3 + [C.c_void_p] * 10 + [fp] * 5 + [C.c_int])
+        L.mxref_multi_lars.argtypes = [C.c_int] + [C.c_void_p] * 5 + [fp] * 3
         L.mxref_multi_sum_sq.argtypes = [C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int]
         L.mxref_sgd_mom_rsp.argtypes = [C.c_int64, C.c_int64] + [C.c_void_p] * 5 + [fp] * 5 + [C.c_int]
         L.mxref_adam_rsp.argtypes = [C.c_int64, C.c_int64] + [C.c_void_p] * 6 + [fp] * 7 + [C.c_int]
@@ -182,6 +183,14 @@ class Oracle:
                                         _pp(weights), sizes.ctypes.data, lrs.ctypes.data, wds.ctypes.data,
                                         etas.ctypes.data, beta1, beta2, eps, rescale, clip, self.nthread)
         assert rc == 0
+
+    def multi_lars(self, lrs, w_sum_sq, g_sum_sq, wds, eta, eps, rescale=1.0):
+        """multi_lars (contrib/multi_lars-inl.h:60-72): layer-wise adapted learning rates."""
+        lrs, w2, g2, wds = _f32(lrs), _f32(w_sum_sq), _f32(g_sum_sq), _f32(wds)
+        out = np.zeros(len(lrs), np.float32)
+        self.lib.mxref_multi_lars(len(lrs), out.ctypes.data, lrs.ctypes.data, w2.ctypes.data, g2.ctypes.data,
+                                  wds.ctypes.data, eta, eps, rescale)
+        return out
 
     def multi_sum_sq(self, arrays):
         out = np.zeros(len(arrays), np.float32)

@@ -16,6 +16,7 @@
 //   CalcSumSq                 src/operator/contrib/multi_sum_sq.cc:68-84
 //   SparseRetainRspThreadKernel src/operator/tensor/sparse_retain-inl.h:121-150
 //   MultiMPAdamWKernel        src/operator/contrib/adamw-inl.h:346-377
+//   MultiLARSKernel           src/operator/contrib/multi_lars-inl.h:60-72
 //   mshadow half_t / Tensor<cpu,1,DType> expressions for the CommCPU reduce
 //                             (restated driver: src/kvstore/comm.h:357-410)
 #include <cstdint>
@@ -27,6 +28,7 @@
 #include "operator/optimizer_op-inl.h"
 #include "operator/tensor/sparse_retain-inl.h"
 #include "operator/contrib/adamw-inl.h"
+#include "operator/contrib/multi_lars-inl.h"
 // The LAMB step functors and CalcSumSq live in .cc files; pull them in as-is.
 #include "operator/contrib/multi_sum_sq.cc"
 #include "operator/contrib/multi_lamb.cc"
@@ -310,6 +312,12 @@ int mxref_multi_adamw(int dtype, int has_mp, int count, void** weights, void** g
                                        beta1, beta2, eps, rescale, clip, nthread);
   else
     return -1;
+  return 0;
+}
+
+int mxref_multi_lars(int n, float* out, const float* lrs, const float* w2, const float* g2,
+                     const float* wds, float eta, float eps, float rescale) {
+  for (int i = 0; i < n; ++i) MultiLARSKernel::Map(i, out, lrs, w2, g2, wds, eta, eps, rescale, kWriteTo);
   return 0;
 }
 

@@ -56,3 +56,38 @@ def test_multi_all_finite_and_reset_arrays(dt):
     assert out.item() == 0.0
     ops.reset_arrays(arrs)
     assert all((a == 0).all() for a in arrs)
+
+
+def test_multi_lars_and_preloaded_sgd(oracle):
+    """LARS recipe (test_operator_gpu.py:307-456): multi_sum_sq -> multi_lars -> preloaded_multi_sgd_mom.
+    multi_lars and the preloaded update are bit-exact given the same inputs; the sums of squares
+    are tree-reduced on the GPU, so the end-to-end chain is compared at rtol 1e-5 / atol 1e-6."""
+    from mxnet_maintenance_b200 import ops
+    rng = np.random.default_rng(51)
+    n = len(SIZES)
+    w = [rng.uniform(-1, 1, s).astype(np.float32) for s in SIZES]
+    g = [(rng.uniform(-1, 1, s) * 1e-2).astype(np.float32) for s in SIZES]
+    g[1][:] = 0                                                    # a zero-gradient layer: lr unchanged
+    lrs = rng.uniform(0.01, 0.2, n).astype(np.float32)
+    wds = rng.uniform(0, 1e-3, n).astype(np.float32)
+    w2, g2 = oracle.multi_sum_sq(w), oracle.multi_sum_sq(g)
+    ref_lrs = oracle.multi_lars(lrs, w2, g2, wds, 0.001, 1e-8, 0.5)
+    t = lambda a: torch.from_numpy(np.ascontiguousarray(a)).cuda()
+    got_lrs = ops.multi_lars(t(lrs), t(w2), t(g2), t(wds), 0.001, 1e-8, 0.5)
+    assert got_lrs.cpu().numpy().tobytes() == ref_lrs.tobytes()
+    assert ref_lrs[1] == lrs[1]
+    # preloaded update, bit-exact with multi_sgd_mom_update fed the same scalars
+    mom = [np.zeros(s, np.float32) for s in SIZES]
+    dw, dm = _cuda(w), _cuda(mom)
+    ops.preloaded_multi_sgd_update(dw, _cuda(g), got_lrs, t(wds), moms=dm, momentum=0.9, rescale_grad=0.5)
+    wr = [x.copy() for x in w]
+    oracle.multi_sgd(wr, g, mom, None, ref_lrs, wds, 0.9, 0.5, -1.0)
+    for a, b in zip(dw + dm, wr + mom):
+        assert a.cpu().numpy().tobytes() == b.tobytes()
+    # whole chain on the GPU
+    dw2, dm2 = _cuda(w), _cuda([np.zeros(s, np.float32) for s in SIZES])
+    dg = _cuda(g)
+    l2 = ops.multi_lars(t(lrs), ops.multi_sum_sq(dw2), ops.multi_sum_sq(dg), t(wds), 0.001, 1e-8, 0.5)
+    ops.preloaded_multi_sgd_update(dw2, dg, l2, t(wds), moms=dm2, momentum=0.9, rescale_grad=0.5)
+    for a, b in zip(dw2, wr):
+        np.testing.assert_allclose(a.cpu().numpy(), b, rtol=1e-5, atol=1e-6)

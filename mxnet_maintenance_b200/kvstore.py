@@ -49,6 +49,26 @@ def _is_array(x):
         hasattr(x, "to_dlpack_for_read") or hasattr(x, "__dlpack__")
 
 
+def _empty(shape, dtype, device_id):
+    """Uninitialised device array from whichever array library the host process uses: torch in the
+    test / bench harness, ``mx.nd`` inside an MXNet process (dtype: 'float32' | 'int64')."""
+    if torch is not None:
+        return torch.empty(shape, dtype=getattr(torch, dtype), device=torch.device("cuda", device_id))
+    import mxnet as mx   # pragma: no cover - only without torch
+    return mx.nd.empty(shape, ctx=mx.gpu(device_id), dtype=dtype)
+
+
+def _to_numpy(x):
+    return x.cpu().numpy() if torch is not None and isinstance(x, torch.Tensor) else x.asnumpy()
+
+
+def _from_numpy(a, device_id):
+    if torch is not None:
+        return torch.as_tensor(a).to(torch.device("cuda", device_id))
+    import mxnet as mx   # pragma: no cover
+    return mx.nd.array(a, ctx=mx.gpu(device_id), dtype=a.dtype)
+
+
 def _numel(x):
     return int(x.numel()) if hasattr(x, "numel") else int(x.size)
 
@@ -183,6 +203,15 @@ class B200(KVStoreBase):
         self._dense_keys = []
         self._sizes = {}
         self.clip_global_norm = None
+        # auto_batch: gluon.Trainer issues one pushpull PER PARAMETER (trainer.py:392-395).  With
+        # auto_batch the per-key calls are only recorded; once every dense key of the store has
+        # been pushed the whole model runs as ONE fused launch sequence (replayed through a bound
+        # step while the same arrays keep arriving).  Anything else that touches the store
+        # (pull, push of a list, wait, checkpointing) flushes first.  Opt-in, because a caller that
+        # pushes only SOME keys must call flush()/wait() before reading the results.
+        self.auto_batch = os.environ.get("B200KV_AUTO_BATCH", "0") == "1"
+        self._pending = []
+        self._auto_steps = {}
         self._bind_stream()
         if world_size > 1:
             self._init_comm()
@@ -294,6 +323,7 @@ class B200(KVStoreBase):
 
     def push(self, key, value, priority=0):
         """kvstore.py:178-270."""
+        self.flush()
         keys, vals, use_str = _flatten(key, value)
         if vals and _is_rsp(vals[0]):
             return self._push_rsp(keys, vals, use_str, priority)
@@ -306,6 +336,7 @@ class B200(KVStoreBase):
     def pull(self, key, out=None, priority=0, ignore_sparse=True):
         """kvstore.py:272-336.  Row-sparse outs are skipped when ignore_sparse (kvstore_local.h:374-385)."""
         assert out is not None
+        self.flush()
         keys, outs, use_str = _flatten(key, out)
         if ignore_sparse:
             sel = [i for i, o in enumerate(outs) if not _is_rsp(o)]
@@ -319,8 +350,46 @@ class B200(KVStoreBase):
         ptrs, keep = self._handles(outs, True)
         check_call(self._lib.b200kv_pull(self._h, len(keys), ck, ptrs, priority))
 
+    def flush(self):
+        """Run the per-key pushpull calls recorded under auto_batch as one batched step."""
+        if not self._pending:
+            return
+        pend, self._pending = self._pending, []
+        keys = [k for k, _, _ in pend]
+        vals = [v for _, v, _ in pend]
+        outs = [(o if o is not None else v) for _, v, o in pend]
+        flat = []
+        for v, o in zip(vals, outs):
+            flat += list(v) if isinstance(v, (list, tuple)) else [v]
+            flat += list(o) if isinstance(o, (list, tuple)) else [o]
+        sig = (tuple(keys), tuple(map(id, flat)))
+        ptrs = tuple(a.data_ptr() for a in flat) if torch is not None and isinstance(flat[0], torch.Tensor) else None
+        hit = self._auto_steps.get(sig)
+        if hit is not None and hit[1] == ptrs:
+            hit[0]()
+            return
+        for old in self._auto_steps.values():
+            old[0].release()
+        self._auto_steps.clear()
+        auto, self.auto_batch = self.auto_batch, False
+        try:
+            step = self.bind_pushpull(keys, vals, out=outs)     # runs the first replay itself
+            step()
+        finally:
+            self.auto_batch = auto
+        self._auto_steps[sig] = (step, ptrs, flat)               # `flat` keeps the arrays (and their ids) alive
+
     def pushpull(self, key, value, out=None, priority=0):
         """kvstore.py:338-415: push then pull; with out=None the result lands in `value`."""
+        if self.auto_batch and isinstance(key, (int, str)) and key in self._sizes \
+                and not _is_rsp(value if _is_array(value) else value[0]):
+            if any(k == key for k, _, _ in self._pending):
+                self.flush()
+            self._pending.append((key, value, out))
+            if len(self._pending) == len(set(self._dense_keys)):
+                self.flush()
+            return
+        self.flush()
         vkeys, vals, use_str = _flatten(key, value)
         if out is None:
             okeys, outs = vkeys, vals
@@ -427,11 +496,14 @@ class B200(KVStoreBase):
     # ------------------------------------------------------------------ row sparse
     def _init_rsp(self, ckey, v, key):
         """init with a row-sparse value: rows that are absent are zero rows of the table."""
-        dev = torch.device("cuda", self._device)
         shape = tuple(v.shape)
-        table = torch.zeros(shape, dtype=torch.float32, device=dev)
-        if v.indices is not None and _numel(v.indices) > 0:
-            table[v.indices.to(dev).long()] = v.data.to(dev).reshape((-1,) + shape[1:])
+        if torch is not None:
+            dev = torch.device("cuda", self._device)
+            table = torch.zeros(shape, dtype=torch.float32, device=dev)
+            if v.indices is not None and _numel(v.indices) > 0:
+                table[v.indices.to(dev).long()] = v.data.to(dev).reshape((-1,) + shape[1:])
+        else:  # pragma: no cover - MXNet host: densify the RowSparseNDArray
+            table = v.tostype("default")
         ptrs, keep = self._handles([table], False)
         check_call(self._lib.b200kv_init_rsp(self._h, ckey, ptrs[0]))
         self._rsp_shapes[key] = shape
@@ -467,9 +539,8 @@ class B200(KVStoreBase):
         n = C.c_int64()
         check_call(self._lib.b200kv_rsp_merged_size(self._h, ck[0], C.byref(n)))
         shape = self._rsp_shapes[key]
-        dev = torch.device("cuda", self._device)
-        idx = torch.empty(n.value, dtype=torch.int64, device=dev)
-        val = torch.empty((n.value,) + tuple(shape[1:]), dtype=torch.float32, device=dev)
+        idx = _empty((n.value,), "int64", self._device)
+        val = _empty((n.value,) + tuple(shape[1:]), "float32", self._device)
         pi, k1 = self._handles([idx], True)
         pd, k2 = self._handles([val], True)
         check_call(self._lib.b200kv_rsp_merged_copy(self._h, ck[0], pi[0], pd[0]))
@@ -492,14 +563,13 @@ class B200(KVStoreBase):
             "the number of row_ids doesn't match the number of values"
         ck = self._keys(keys, isinstance(keys[0], str))
         self._bind_stream()
-        dev = torch.device("cuda", self._device)
         for k, c, o, ids in zip(keys, ck, first_out, row_ids):
             if not _is_rsp(o):
                 raise B200KVError("row_sparse_pull requires row_sparse outputs")
             shape = self._rsp_shapes[k]
             n = int(ids.numel()) if hasattr(ids, "numel") else int(ids.size)
-            idx = torch.empty(max(n, 1), dtype=torch.int64, device=dev)
-            val = torch.empty((max(n, 1),) + tuple(shape[1:]), dtype=torch.float32, device=dev)
+            idx = _empty((max(n, 1),), "int64", self._device)
+            val = _empty((max(n, 1),) + tuple(shape[1:]), "float32", self._device)
             pr, k0 = self._handles([ids], False)
             pi, k1 = self._handles([idx], True)
             pd, k2 = self._handles([val], True)
@@ -509,7 +579,9 @@ class B200(KVStoreBase):
             o.indices, o.data, o.shape = idx[:nnr.value], val[:nnr.value], shape
         if first_out is not outs:
             for o in outs[1:]:
-                o.indices, o.data, o.shape = outs[0].indices.clone(), outs[0].data.clone(), outs[0].shape
+                o.indices, o.data, o.shape = outs[0].indices.copy() if not hasattr(outs[0].indices, "clone") \
+                    else outs[0].indices.clone(), outs[0].data.copy() if not hasattr(outs[0].data, "clone") \
+                    else outs[0].data.clone(), outs[0].shape
 
     # ------------------------------------------------------------------ optimizer / capabilities
     def set_optimizer(self, optimizer):
@@ -550,6 +622,7 @@ class B200(KVStoreBase):
 
     def wait(self):
         """Block until every enqueued operation has finished (NDArray.wait_to_read on the outs)."""
+        self.flush()
         check_call(self._lib.b200kv_wait(self._h))
 
     def launch_count(self):
@@ -568,19 +641,21 @@ class B200(KVStoreBase):
         (optimizer.py:252-255,583-600,1264-1268,1602-1607): SGD `mom` | `(mom, w32)`;
         Adam/LAMB `(mean, var)` | `(w32, (mean, var))`.  Collective when num_workers > 1."""
         assert self._updater is not None
+        self.flush()
         kind = opt_mod.kind_of(self._updater.optimizer)
         states = {}
-        dev = torch.device("cuda", self._device)
         for key in dict.fromkeys(self._dense_keys):
             ck = self._keys([key], isinstance(key, str))
             got = []
             for which in (0, 1, 2):
                 n = self._key_size(key)
-                buf = torch.empty(n, dtype=torch.float32, device=dev)
+                buf = _empty((n,), "float32", self._device)
                 p, keep = self._handles([buf], True)
                 present = C.c_int()
                 check_call(self._lib.b200kv_get_state(self._h, ck[0], which, p[0], C.byref(present)))
-                got.append(buf.cpu().numpy() if present.value else None)
+                if present.value:
+                    check_call(self._lib.b200kv_wait(self._h))
+                got.append(_to_numpy(buf) if present.value else None)
             s0, s1, w32 = got
             if s0 is None and s1 is None and w32 is None and kind != "sgd":
                 continue
@@ -611,7 +686,7 @@ class B200(KVStoreBase):
         self._opt_sent = None
         self._send_optimizer()
         kind = opt_mod.kind_of(self._updater.optimizer)
-        dev = torch.device("cuda", self._device)
+        import numpy as _np
         for key, st in self._updater.states.items():
             if kind == "sgd":
                 s0, s1, w32 = (st[0], None, st[1]) if isinstance(st, tuple) else (st, None, None)
@@ -623,7 +698,7 @@ class B200(KVStoreBase):
             for which, arr in ((2, w32), (0, s0), (1, s1)):
                 if arr is None:
                     continue
-                t = torch.as_tensor(arr, dtype=torch.float32).reshape(-1).to(dev)
+                t = _from_numpy(_np.ascontiguousarray(_np.asarray(arr, dtype=_np.float32).reshape(-1)), self._device)
                 p, keep = self._handles([t], False)
                 check_call(self._lib.b200kv_set_state(self._h, ck[0], which, p[0]))
         self.wait()

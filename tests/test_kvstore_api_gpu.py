@@ -206,3 +206,42 @@ def test_pull_ignores_row_sparse_outs():
     assert rsp.data is None
     with pytest.raises(m.B200KVError):
         kv.pull(3, out=rsp, ignore_sparse=False)
+
+
+def test_auto_batch_per_key_trainer_loop(oracle=None):
+    """gluon.Trainer's per-parameter loop (trainer.py:392-395: pushpull(i, grads, out=weights,
+    priority=-i)) under auto_batch: the calls are fused into one launch per step and give the same
+    bits as immediate per-key calls."""
+    m = mb()
+    from mxnet_maintenance_b200 import shapes
+    shp = shapes.mlp() + [(33,), (4097,)]
+    rng = np.random.default_rng(3)
+    w0 = [rng.uniform(-1, 1, s).astype(np.float32) for s in shp]
+    gs = [[(rng.uniform(-1, 1, s) * 1e-2).astype(np.float32) for s in shp] for _ in range(4)]
+    res, launches = [], []
+    for auto in (False, True):
+        kv = m.create("b200")
+        kv.auto_batch = auto
+        kv.set_optimizer(m.optimizer.SGD(learning_rate=0.1, momentum=0.9, wd=1e-4))
+        w = [torch.from_numpy(x).cuda() for x in w0]
+        g = [torch.empty_like(x) for x in w]                     # persistent gradient buffers
+        for i, x in enumerate(w):
+            kv.broadcast(i, x, out=[x])
+        kv.wait()
+        base = kv.launch_count()
+        for it in range(4):
+            for d, h in zip(g, gs[it]):
+                d.copy_(torch.from_numpy(h))
+            for i in range(len(w)):
+                kv.pushpull(i, [g[i]], out=[w[i]], priority=-i)
+        kv.wait()
+        launches.append(kv.launch_count() - base)
+        res.append([x.cpu().numpy() for x in w])
+    for a, b in zip(*res):
+        assert a.tobytes() == b.tobytes()
+    assert launches[0] == 4 * len(shp) and launches[1] == 4     # one fused launch per step
+    # a partial set of keys is executed at the next flush point (wait / pull / ...)
+    kv.pushpull(0, [g[0]], out=[w[0]])
+    before = w[0].clone()
+    kv.wait()
+    assert not torch.equal(before, w[0])

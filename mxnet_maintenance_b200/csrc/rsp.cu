@@ -64,11 +64,17 @@ int sort_pairs(RspKey& k, int n, cudaStream_t st, int64_t* launches) {
   int flips = 0;
   for (int shift = 0; shift < k.bits; shift += 8) {
     radix_hist_kernel<<<nblocks, kSortThreads, 0, st>>>(ka, n, shift, k.counts.as<uint32_t>(), nblocks);
-    scan_small_kernel<<<1, 1024, 0, st>>>(k.counts.as<uint32_t>(), 256 * nblocks);
-    radix_scatter_kernel<<<nblocks, kSortThreads, 0, st>>>(ka, pa, kb, pb, n, shift,
-                                                            k.counts.as<uint32_t>(), nblocks);
+    if (nblocks <= 256) {   // each scatter CTA derives its offsets from the raw counts itself
+      radix_scatter_kernel<false><<<nblocks, kSortThreads, 0, st>>>(ka, pa, kb, pb, n, shift,
+                                                                   k.counts.as<uint32_t>(), nblocks);
+      *launches += 2;
+    } else {
+      scan_small_kernel<<<1, 1024, 0, st>>>(k.counts.as<uint32_t>(), 256 * nblocks);
+      radix_scatter_kernel<true><<<nblocks, kSortThreads, 0, st>>>(ka, pa, kb, pb, n, shift,
+                                                                  k.counts.as<uint32_t>(), nblocks);
+      *launches += 3;
+    }
     CUDA_OK(cudaGetLastError());
-    *launches += 3;
     std::swap(ka, kb);
     std::swap(pa, pb);
     ++flips;
@@ -80,11 +86,17 @@ int sort_pairs(RspKey& k, int n, cudaStream_t st, int64_t* launches) {
 void unique_heads(RspKey& k, const uint32_t* keys, int n, cudaStream_t st, int64_t* launches) {
   const int nb = (n + kScanTile - 1) / kScanTile;
   head_count_kernel<<<nb, 256, 0, st>>>(keys, n, k.bsum.as<uint32_t>());
-  scan_small_kernel<<<1, 1024, 0, st>>>(k.bsum.as<uint32_t>(), nb);
-  head_write_kernel<<<nb, 256, 0, st>>>(keys, n, k.bsum.as<uint32_t>(), k.uniq.as<int64_t>(),
-                                        k.seg_start.as<int32_t>(), k.count.as<int64_t>(), nb);
+  if (nb <= 2048) {
+    head_write_kernel<false><<<nb, 256, 0, st>>>(keys, n, k.bsum.as<uint32_t>(), k.uniq.as<int64_t>(),
+                                                 k.seg_start.as<int32_t>(), k.count.as<int64_t>(), nb);
+    *launches += 2;
+  } else {
+    scan_small_kernel<<<1, 1024, 0, st>>>(k.bsum.as<uint32_t>(), nb);
+    head_write_kernel<true><<<nb, 256, 0, st>>>(keys, n, k.bsum.as<uint32_t>(), k.uniq.as<int64_t>(),
+                                                k.seg_start.as<int32_t>(), k.count.as<int64_t>(), nb);
+    *launches += 3;
+  }
   CUDA_OK(cudaGetLastError());
-  *launches += 3;
 }
 
 }  // namespace

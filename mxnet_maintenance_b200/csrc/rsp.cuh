@@ -97,12 +97,42 @@ __global__ void __launch_bounds__(1024) scan_small_kernel(uint32_t* __restrict__
 
 // stable scatter: rank of a key = #equal digits before it (global offset of its CTA + earlier
 // warps of the CTA + earlier positions inside its warp segment, by __match_any_sync)
+// SCANNED: `offsets` already holds the exclusive scan of the digit-major count matrix (large inputs);
+// otherwise it holds the raw counts and each CTA derives its own offsets (one launch fewer — the
+// matrix is a few thousand words for the row-id lists this path sees).
+template <bool SCANNED>
 __global__ void __launch_bounds__(kSortThreads)
 radix_scatter_kernel(const uint32_t* __restrict__ keys_in, const uint32_t* __restrict__ pay_in,
                      uint32_t* __restrict__ keys_out, uint32_t* __restrict__ pay_out, int n, int shift,
                      const uint32_t* __restrict__ offsets, int nblocks) {
   __shared__ uint32_t wcount[kSortThreads / 32][256];
+  __shared__ uint32_t dscan[8];
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  uint32_t my_offset;
+  if (SCANNED) {
+    my_offset = offsets[tid * nblocks + blockIdx.x];
+  } else {
+    // digit `tid`: keys with this digit in earlier CTAs, and in all CTAs
+    uint32_t before = 0, total = 0;
+    const uint32_t* row = offsets + tid * nblocks;
+    for (int b = 0; b < nblocks; ++b) {
+      const uint32_t c = row[b];
+      total += c;
+      if (b < static_cast<int>(blockIdx.x)) before += c;
+    }
+    // exclusive scan of `total` over the 256 digits
+    uint32_t x = total;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const uint32_t y = __shfl_up_sync(0xffffffffu, x, o);
+      if (lane >= o) x += y;
+    }
+    if (lane == 31) dscan[warp] = x;
+    __syncthreads();
+    uint32_t base = x - total;
+    for (int w = 0; w < warp; ++w) base += dscan[w];
+    my_offset = base + before;
+  }
   for (int i = tid; i < (kSortThreads / 32) * 256; i += kSortThreads) (&wcount[0][0])[i] = 0;
   __syncthreads();
   constexpr int kRounds = kSortTile / kSortThreads;   // 16
@@ -127,7 +157,7 @@ radix_scatter_kernel(const uint32_t* __restrict__ keys_in, const uint32_t* __res
   }
   __syncthreads();
   {  // digit `tid`: exclusive prefix over the warps, seeded with this CTA's global offset
-    uint32_t run = offsets[tid * nblocks + blockIdx.x];
+    uint32_t run = my_offset;
 #pragma unroll
     for (int w = 0; w < kSortThreads / 32; ++w) {
       const uint32_t t = wcount[w][tid];
@@ -173,12 +203,30 @@ head_count_kernel(const uint32_t* __restrict__ keys, int n, uint32_t* __restrict
 }
 
 // after scan_small_kernel(bsum): bsum[b] = heads before tile b; count[0] = total number of heads
+template <bool SCANNED>
 __global__ void __launch_bounds__(256)
 head_write_kernel(const uint32_t* __restrict__ keys, int n, const uint32_t* __restrict__ bsum,
                   int64_t* __restrict__ uniq, int32_t* __restrict__ seg_start, int64_t* __restrict__ count,
                   int nb) {
   __shared__ uint32_t ws[8];
+  __shared__ uint32_t tile_base;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  if (SCANNED) {
+    if (tid == 0) tile_base = bsum[blockIdx.x];
+  } else {
+    uint32_t part = 0;
+    for (int b = tid; b < static_cast<int>(blockIdx.x); b += 256) part += bsum[b];
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) part += __shfl_down_sync(0xffffffffu, part, o);
+    if (lane == 0) ws[warp] = part;
+    __syncthreads();
+    if (tid == 0) {
+      uint32_t t = 0;
+      for (int w = 0; w < 8; ++w) t += ws[w];
+      tile_base = t;
+    }
+  }
+  __syncthreads();
   const int i0 = blockIdx.x * kScanTile + tid * 4;   // 4 consecutive keys per thread
   bool h[4];
   uint32_t c = 0;
@@ -195,7 +243,7 @@ head_write_kernel(const uint32_t* __restrict__ keys, int n, const uint32_t* __re
   }
   if (lane == 31) ws[warp] = x;
   __syncthreads();
-  uint32_t pos = bsum[blockIdx.x] + x - c;
+  uint32_t pos = tile_base + x - c;
   for (int w = 0; w < warp; ++w) pos += ws[w];
 #pragma unroll
   for (int j = 0; j < 4; ++j)

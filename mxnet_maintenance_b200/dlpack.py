@@ -10,7 +10,6 @@ The capsule stays owned by Python: the library only borrows the struct for the d
 and never invokes its deleter, so an un-consumed capsule frees itself normally.
 """
 import ctypes as C
-import weakref
 
 _PyCapsule_GetPointer = C.pythonapi.PyCapsule_GetPointer
 _PyCapsule_GetPointer.restype = C.c_void_p
@@ -40,25 +39,12 @@ def pointer_of(capsule):
 
 
 class HandleCache:
-    """Caches one DLPack export per live torch tensor (keyed by id, validated by a weak reference
-    and the current data pointer) so a steady-state step does not re-export hundreds of tensors.
-    MXNet NDArrays are never cached: their getters double as engine synchronisation points."""
-
-    def __init__(self):
-        self._c = {}
+    """Exports arrays for one call.  Nothing is retained between calls: a DLPack capsule owns a
+    reference to the tensor (PyTorch even keeps the Python object alive through it), so caching
+    capsules would pin every temporary ever passed in.  Steady-state training does not pay the
+    per-call export: ``B200.bind_pushpull`` exports once and keeps the capsules for as long as the
+    step stays bound."""
 
     def get(self, arr, for_write=False):
-        if _torch is None or not isinstance(arr, _torch.Tensor):
-            cap = capsule_of(arr, for_write)
-            return pointer_of(cap), cap
-        key = id(arr)
-        hit = self._c.get(key)
-        ptr = arr.data_ptr()
-        if hit is not None and hit[0]() is arr and hit[1] == ptr and hit[4] == arr.shape:
-            return hit[3], hit[2]
-        cap = _torch_to_dlpack(arr)
-        p = pointer_of(cap)
-        if len(self._c) > 65536:
-            self._c.clear()
-        self._c[key] = (weakref.ref(arr), ptr, cap, p, arr.shape)
-        return p, cap
+        cap = capsule_of(arr, for_write)
+        return pointer_of(cap), cap

@@ -245,3 +245,24 @@ def test_auto_batch_per_key_trainer_loop(oracle=None):
     before = w[0].clone()
     kv.wait()
     assert not torch.equal(before, w[0])
+
+
+def test_handle_cache_does_not_pin_temporaries():
+    """Exported DLPack capsules hold a reference to the tensor storage; the per-store handle cache
+    must let go of them when the tensor dies (row_sparse_pull allocates fresh outputs every call)."""
+    import gc
+    m = mb()
+    kv = m.create("b200")
+    w = torch.zeros(1 << 20, device="cuda")
+    kv.init(0, w)
+    torch.cuda.synchronize()
+    gc.collect()
+    base = torch.cuda.memory_allocated()
+    for _ in range(20):
+        t = torch.empty(8 << 20, device="cuda")          # 32 MB temporary pulled into
+        kv.pull(0, out=torch.empty(1 << 20, device="cuda"))
+        kv._handles([t], True)
+        del t
+    kv.wait()
+    gc.collect()
+    assert torch.cuda.memory_allocated() - base < (40 << 20)

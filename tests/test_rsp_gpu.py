@@ -162,3 +162,17 @@ def test_c5_full_size(oracle):
     pos = np.searchsorted(rows, midx).astype(np.int64)
     oracle.sgd_mom_rsp(sub, mom, pos, mval, 0.1, 1e-4, 0.9)
     assert pv.tobytes() == sub[np.searchsorted(rows, uniq)].tobytes()
+
+
+def test_pull_with_millions_of_ids(oracle):
+    """> 1M / > 2M ids exercise the separate-scan variants of the sort and unique kernels."""
+    rng = np.random.default_rng(77)
+    num_rows, row_len = 300000, 4
+    table = rng.uniform(-1, 1, (num_rows, row_len)).astype(np.float32)
+    kv, mb = _kv(table)
+    for n in (1_100_000, 2_300_000):
+        ids = rng.integers(0, num_rows, n)
+        pi, pv = _pull(kv, mb, torch.from_numpy(ids).cuda())
+        uniq = np.unique(ids).astype(np.int64)
+        assert pi.tobytes() == uniq.tobytes()
+        assert pv.tobytes() == table[uniq].tobytes()

@@ -8,7 +8,7 @@
  * compiled from /root/reference (oracle/_ref/libmxref.so, see oracle/ref_shim.cc) in
  * tests/test_oracle_vs_ref.py, and against committed golden vectors generated from those functors
  * (tests/golden/, generator tests/golden/make_golden.py) plus the closed-form known answers the
- * reference's own tests hold (tests/test_known_answers.py).
+ * reference's own tests hold (tests/test_host_logic.py, tests/test_kvstore_api_gpu.py).
  *
  * All arithmetic is IEEE fp32 with no contraction (-ffp-contract=off) in the reference's evaluation
  * order; fp16 goes through F16C round-to-nearest-even exactly as mshadow::half::half_t does

@@ -355,3 +355,64 @@ def test_uneven_copy_counts_in_one_call(oracle):
         kv.wait()
         for k in range(3):
             assert dev[k].cpu().numpy().tobytes() == model.pushpull(k, g[k]).tobytes()
+
+
+def test_bert_large_lamb_clip_full_size(oracle):
+    """C4 at full size (391 arrays, 335,141,888 parameters): one LAMB step with clip_global_norm on
+    the store vs the oracle (clip_global_norm restatement + the reference's MultiLAMB functors).
+    Weights within the north-star fp32 tolerance; the global norm and the per-tensor sums of
+    squares are also checked against a float64 truth (the CPU reference accumulates 31M-element
+    tensors sequentially in fp32, the GPU reduces pairwise — SURVEY.md Appendix A.4)."""
+    import mxnet_maintenance_b200 as mb
+    from mxnet_maintenance_b200 import shapes, ops
+    shp = shapes.bert_large()
+    keys = list(range(len(shp)))
+    rng = np.random.default_rng(4)
+    w0 = [rng.uniform(-1, 1, s).astype(np.float32) for s in shp]
+    g0 = [(rng.uniform(-1, 1, s) * 1e-2).astype(np.float32) for s in shp]
+    kv = mb.create("b200")
+    kv.set_optimizer(mb.optimizer.LAMB(learning_rate=1e-3, beta1=0.9, beta2=0.999, epsilon=1e-6, wd=0.01))
+    kv.clip_global_norm = 1.0
+    dev_w = [torch.from_numpy(w).cuda() for w in w0]
+    dev_g = [torch.from_numpy(g).cuda() for g in g0]
+    kv.broadcast(keys, dev_w, [[w] for w in dev_w])
+    kv.pushpull(keys, dev_g, out=[[w] for w in dev_w])
+    kv.wait()
+    truth_norm = float(np.sqrt(sum(float((g.astype(np.float64) ** 2).sum()) for g in g0)))
+    assert abs(kv.last_global_norm() - truth_norm) <= 2e-6 * truth_norm
+    # sums of squares of the largest tensor: GPU tree reduction vs float64
+    big = int(np.argmax([shapes.numel(s) for s in shp]))
+    ss = ops.multi_sum_sq([dev_g[big]]).item()
+    t64 = float((g0[big].astype(np.float64) ** 2).sum())
+    assert abs(ss - t64) <= 1e-6 * t64
+    # oracle step (reference CPU functors: sums of squares accumulated sequentially in fp32)
+    gc = [g.copy().reshape(-1) for g in g0]
+    oracle.clip_global_norm(gc, 1.0)
+    wr = [w.copy().reshape(-1) for w in w0]
+    me = [np.zeros(w.size, np.float32) for w in w0]
+    va = [np.zeros(w.size, np.float32) for w in w0]
+    oracle.multi_lamb(wr, gc, me, va, None, [1e-3] * len(shp), [0.01] * len(shp), [1] * len(shp), eps=1e-6)
+    f = np.float32
+    worst_gpu = worst_cpu = 0.0
+    for k in keys:
+        got = dev_w[k].cpu().numpy().reshape(-1)
+        if w0[k].size <= (1 << 20):
+            # up to ~1M elements the CPU's sequential fp32 sums are still accurate: direct parity
+            np.testing.assert_allclose(got, wr[k], rtol=RTOL32, atol=ATOL32, err_msg="key %d" % k)
+            continue
+        # Larger tensors: the CPU kernel's `sum += x*x` in fp32 stalls once the sum dwarfs the addends
+        # (multi_sum_sq.cc:68-84), so its trust ratio is off by far more than the tolerance.  Adjudicate
+        # with the same fp32 elementwise step-1 math and float64-accurate norms.
+        w, g = w0[k].reshape(-1), gc[k]
+        b1, b2, eps, wd, lr = f(0.9), f(0.999), f(1e-6), f(0.01), f(1e-3)
+        m = b1 * f(0) + (f(1) - b1) * g
+        v = b2 * f(0) + ((f(1) - b2) * g) * g
+        u = (m / (f(1) - b1)) / (np.sqrt(v / (f(1) - b2)) + eps) + wd * w
+        r1 = np.sqrt(f((w.astype(np.float64) ** 2).sum()))
+        r2 = np.sqrt(f((u.astype(np.float64) ** 2).sum()))
+        truth = w - (lr * (r1 / r2)) * u
+        np.testing.assert_allclose(got, truth, rtol=RTOL32, atol=ATOL32, err_msg="key %d vs float64 norms" % k)
+        worst_gpu = max(worst_gpu, float(np.abs(got - truth).max()))
+        worst_cpu = max(worst_cpu, float(np.abs(wr[k] - truth).max()))
+    # the GPU path is closer to the exact-norm result than the CPU reference on every big tensor
+    assert worst_gpu < 1e-6 and worst_gpu < worst_cpu

@@ -52,6 +52,9 @@ int launch_scale(const MtaCall& c, const float* gscale);
 // out copies (dtype) <- W section (fp32 master)
 int launch_master_to_out(const MtaCall& c);
 
+// push slice r of `src` (this rank's bucket, `slice_bytes` per slice) into dst[r] for every r != rank
+int launch_p2p_push(const void* src, void* const* dst, int64_t slice_bytes, int world, int rank, int device,
+                    cudaStream_t stream);
 // stand-alone peer-memory barrier kernel (see optim.cuh): which = 0 "gradients ready",
 // 1 "weights written"; used around the TMA-staged kernels, which carry no in-kernel barrier
 int launch_p2p_barrier(const P2PFlags& f, int which, cudaStream_t stream);

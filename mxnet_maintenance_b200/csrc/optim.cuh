@@ -572,6 +572,43 @@ mta_kernel(const MtaArgs a, const Op op, const float* __restrict__ gscale,
 // on different GPUs, so waiting here cannot starve the signaller.  A bounded spin (~20 s) turns a
 // lost peer into an error flag instead of a hung GPU.
 // ------------------------------------------------------------------------------------------------
+// Reduce-scatter, push half: every rank stores slice r of its own gradient bucket into rank r's
+// staging area (region `rank` of it).  Pure NVLink writes — measured 677 GB/s per direction with
+// both directions busy, against 624 GB/s for peer reads and ~590 GB/s for mixed read+write traffic.
+// dst[r] = rank r's staging region for this rank (nullptr for r == rank); 16-byte vectors.
+struct PushArgs {
+  uint4* dst[kMaxCopies];
+  const uint4* src;        // this rank's bucket
+  int64_t slice_vecs;      // 16-byte vectors per slice
+  int world, rank;
+};
+
+static __global__ void __launch_bounds__(256) p2p_push_kernel(const PushArgs a) {
+  // tile = 256 threads x 4 vectors (16 KB); tiles are dealt round-robin over the W-1 peers so that
+  // all links carry traffic all the time
+  constexpr int kVecPerTile = 1024;
+  const int npeer = a.world - 1;
+  const int64_t tiles_per_slice = (a.slice_vecs + kVecPerTile - 1) / kVecPerTile;
+  const int64_t ntiles = tiles_per_slice * npeer;
+  for (int64_t t = blockIdx.x; t < ntiles; t += gridDim.x) {
+    const int pi = static_cast<int>(t % npeer);
+    const int r = pi < a.rank ? pi : pi + 1;
+    const int64_t v0 = (t / npeer) * kVecPerTile;
+    const uint4* src = a.src + static_cast<int64_t>(r) * a.slice_vecs;
+    uint4 x[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const int64_t v = v0 + u * 256 + threadIdx.x;
+      if (v < a.slice_vecs) x[u] = src[v];
+    }
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const int64_t v = v0 + u * 256 + threadIdx.x;
+      if (v < a.slice_vecs) a.dst[r][v] = x[u];
+    }
+  }
+}
+
 // which = 0: ready slots, 1: done slots.  flags block layout: [0..8) ready, [8..16) done, [16] error
 static __global__ void p2p_barrier_kernel(const P2PFlags f, int which) {
   const int k = threadIdx.x;

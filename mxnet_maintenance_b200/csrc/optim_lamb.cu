@@ -1,0 +1,30 @@
+// Host launchers (one kernel family per translation unit, see launch_impl.cuh).
+#include "launch_impl.cuh"
+
+namespace b200kv {
+
+int launch_lamb1(const MtaCall& c, const OptScalars& s, const float* gscale, float* partials) {
+  Lamb1Op op{s.beta1, s.beta2, s.eps, s.rescale, s.clip, s.bias_correction};
+  return launch_update(c, op, gscale, partials);
+}
+
+int launch_lamb2(const MtaCall& c, const OptScalars& s, const float* ratio) {
+  Lamb2Op op{s.eps, s.bias_correction, ratio};
+  return launch_update(c, op, nullptr, nullptr);
+}
+
+int launch_sumsq(const MtaCall& c, float* partials) {
+  SumSqOp op;
+  if (c.dtype == kF32) return launch_ng<SumSqOp, float, float>(c, op, nullptr, partials);
+  KV_CHECK(c.dtype == kF16, "unsupported dtype " << c.dtype);
+  return launch_ng<SumSqOp, __half, __half>(c, op, nullptr, partials);
+}
+
+int launch_nonfinite(const MtaCall& c, float* partials) {
+  NonFiniteOp op;
+  if (c.dtype == kF32) return launch_ng<NonFiniteOp, float, float>(c, op, nullptr, partials);
+  KV_CHECK(c.dtype == kF16, "unsupported dtype " << c.dtype);
+  return launch_ng<NonFiniteOp, __half, __half>(c, op, nullptr, partials);
+}
+
+}  // namespace b200kv

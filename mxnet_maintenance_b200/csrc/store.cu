@@ -68,6 +68,7 @@ Store::~Store() {
       if (P.g[k]) cudaIpcCloseMemHandle(P.g[k]);
       if (P.w[k]) cudaIpcCloseMemHandle(P.w[k]);
       if (P.flags[k]) cudaIpcCloseMemHandle(P.flags[k]);
+      if (P.stage[k]) cudaIpcCloseMemHandle(P.stage[k]);
     }
   }
   for (auto& e : prof_events_) {
@@ -614,7 +615,9 @@ void Store::setup_p2p(Segment& s) {
   Segment::P2P& P = s.p2p;
   NcclApi& nccl = NcclApi::get();
   ncclComm_t comm = reinterpret_cast<ncclComm_t>(comm_);
-  struct Handles { cudaIpcMemHandle_t g, w, f; };
+  struct Handles { cudaIpcMemHandle_t g, w, f, s; };
+  const size_t seg_bytes = static_cast<size_t>(s.total) * dtype_size(s.dtype);
+  P.local_stage.reserve(std::max<size_t>(seg_bytes, 2u << 20));
   P.local_flags.reserve(2u << 20);   // its own 2 MiB allocation: IPC maps whole allocations
   CUDA_OK(cudaMemsetAsync(P.local_flags.p, 0, 256, stream_));
   Handles mine;
@@ -622,6 +625,7 @@ void Store::setup_p2p(Segment& s) {
   if (cudaIpcGetMemHandle(&mine.g, s.gbuf.p) != cudaSuccess) ok = 0;
   if (cudaIpcGetMemHandle(&mine.w, s.wbuf.p) != cudaSuccess) ok = 0;
   if (cudaIpcGetMemHandle(&mine.f, P.local_flags.p) != cudaSuccess) ok = 0;
+  if (cudaIpcGetMemHandle(&mine.s, P.local_stage.p) != cudaSuccess) ok = 0;
   (void)cudaGetLastError();
   DevBuf stage;
   const size_t hb = sizeof(Handles);
@@ -635,12 +639,14 @@ void Store::setup_p2p(Segment& s) {
   for (int k = 0; k < world_ && ok; ++k) {
     if (k == rank_) {
       P.g[k] = s.gbuf.p; P.w[k] = s.wbuf.p; P.flags[k] = P.local_flags.as<uint32_t>();
+      P.stage[k] = P.local_stage.p;
       continue;
     }
     void* f = nullptr;
     if (cudaIpcOpenMemHandle(&P.g[k], all[k].g, cudaIpcMemLazyEnablePeerAccess) != cudaSuccess ||
         cudaIpcOpenMemHandle(&P.w[k], all[k].w, cudaIpcMemLazyEnablePeerAccess) != cudaSuccess ||
-        cudaIpcOpenMemHandle(&f, all[k].f, cudaIpcMemLazyEnablePeerAccess) != cudaSuccess)
+        cudaIpcOpenMemHandle(&f, all[k].f, cudaIpcMemLazyEnablePeerAccess) != cudaSuccess ||
+        cudaIpcOpenMemHandle(&P.stage[k], all[k].s, cudaIpcMemLazyEnablePeerAccess) != cudaSuccess)
       ok = 0;
     P.flags[k] = static_cast<uint32_t*>(f);
   }
@@ -668,7 +674,8 @@ void Store::setup_p2p(Segment& s) {
       if (P.g[k]) cudaIpcCloseMemHandle(P.g[k]);
       if (P.w[k]) cudaIpcCloseMemHandle(P.w[k]);
       if (P.flags[k]) cudaIpcCloseMemHandle(P.flags[k]);
-      P.g[k] = P.w[k] = nullptr; P.flags[k] = nullptr;
+      if (P.stage[k]) cudaIpcCloseMemHandle(P.stage[k]);
+      P.g[k] = P.w[k] = P.stage[k] = nullptr; P.flags[k] = nullptr;
     }
 }
 
@@ -688,7 +695,18 @@ void Store::run_class_p2p(DensePlan& p, Segment& s, const std::vector<const Entr
   // into the local bucket once instead of crossing NVLink on every pass
   const bool prereduce = opt_.kind == B200KV_OPT_LAMB || opt_.clip_global_norm >= 0.f;
   static const bool staged_env = [] { const char* e = getenv("B200KV_STAGED"); return e && e[0] == '1'; }();
+  static const bool push_env = [] { const char* e = getenv("B200KV_PUSH"); return !(e && e[0] == '0'); }();
   const bool staged = staged_env;
+  // Reduce-scatter half: PUSH (default) — every rank first stores the slices of its bucket into
+  // their owners' staging areas (NVLink writes only), then the owner sums W local copies; or PULL —
+  // the owner loads its shard of every peer's bucket directly inside the fused kernel.
+  const bool push_rs = push_env && !staged;
+  // gradient copy k of the element at flat offset `off`, as seen by the shard owner
+  auto grad_src = [&](int k, int64_t off) -> const char* {
+    if (!push_rs) return static_cast<const char*>(P.g[k]) + off * es;
+    if (k == rank_) return static_cast<const char*>(s.gbuf.p) + off * es;
+    return static_cast<const char*>(P.local_stage.p) + (static_cast<int64_t>(k) * s.slice + off - rank_ * s.slice) * es;
+  };
   const int upd_ng = prereduce ? 1 : W, upd_no = mp ? W : W - 1;
   const size_t w_pack = mta_blob_words(nt, ng, 0), w_pre = prereduce ? mta_blob_words(nt, W, 0) : 0,
                w_upd = mta_blob_words(nt, upd_ng, upd_no), w_unpack = mta_blob_words(nt, 1, no);
@@ -705,7 +723,7 @@ void Store::run_class_p2p(DensePlan& p, Segment& s, const std::vector<const Entr
     Blob b(host + o_pre, nt, W, 0);
     for (int t = 0; t < nt; ++t) {
       const int64_t off = keys_[p.keys[t]].off;
-      for (int k = 0; k < W; ++k) b.G(k, t, static_cast<char*>(P.g[k]) + off * es);
+      for (int k = 0; k < W; ++k) b.G(k, t, grad_src(k, off));
       b.S(kSecW, t, at(s.gbuf, off, es));
     }
   }
@@ -714,7 +732,7 @@ void Store::run_class_p2p(DensePlan& p, Segment& s, const std::vector<const Entr
     for (int t = 0; t < nt; ++t) {
       const KeyInfo& ki = keys_[p.keys[t]];
       if (prereduce) u.G(0, t, at(s.gbuf, ki.off, es));
-      else for (int k = 0; k < W; ++k) u.G(k, t, static_cast<char*>(P.g[k]) + ki.off * es);
+      else for (int k = 0; k < W; ++k) u.G(k, t, grad_src(k, ki.off));
       int o = 0;
       for (int k = 0; k < W; ++k) {
         if (!mp && k == rank_) continue;   // fp32: the W section already is the local weight buffer
@@ -752,8 +770,18 @@ void Store::run_class_p2p(DensePlan& p, Segment& s, const std::vector<const Entr
   P2PFlags f;
   for (int k = 0; k < kMaxCopies; ++k) f.flags[k] = P.flags[k];
   f.world = W; f.rank = rank_; f.epoch = ++P.epoch;
-  // Barriers: folded into the first peer-reading / last peer-writing kernel (plain kernels), or
-  // separate one-warp kernels (TMA-staged kernels).
+  if (push_rs) {
+    void* dst[kMaxCopies] = {nullptr};
+    for (int k = 0; k < W; ++k)
+      if (k != rank_) dst[k] = static_cast<char*>(P.stage[k]) + static_cast<int64_t>(rank_) * s.slice * es;
+    prof_begin(1);
+    launches_ += launch_p2p_push(s.gbuf.p, dst, s.slice * static_cast<int64_t>(es), W, rank_, device_, stream_);
+    prof_end();
+  }
+  // Barriers: folded into the first kernel that reads the exchanged gradients / the last one that
+  // writes peer weights (plain kernels), or separate one-warp kernels (TMA-staged kernels).  With
+  // the push reduce-scatter "ready" means "my pushes have landed" (the push kernel precedes the
+  // signalling kernel in stream order).
   const bool fold = !staged;
   const P2PFlags* dsync = P.dev_sync.as<P2PFlags>();
   prof_begin(2);

@@ -48,6 +48,8 @@ struct Segment {
     void* g[kMaxCopies] = {nullptr};
     void* w[kMaxCopies] = {nullptr};
     uint32_t* flags[kMaxCopies] = {nullptr};
+    void* stage[kMaxCopies] = {nullptr};   // every rank's staging area ([world][slice], push reduce-scatter)
+    DevBuf local_stage;
     DevBuf local_flags;
     DevBuf dev_sync;     // P2PFlags resident on the device for the in-kernel barriers
     uint32_t epoch = 0;

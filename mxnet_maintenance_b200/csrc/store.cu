@@ -695,11 +695,12 @@ void Store::run_class_p2p(DensePlan& p, Segment& s, const std::vector<const Entr
   // into the local bucket once instead of crossing NVLink on every pass
   const bool prereduce = opt_.kind == B200KV_OPT_LAMB || opt_.clip_global_norm >= 0.f;
   static const bool staged_env = [] { const char* e = getenv("B200KV_STAGED"); return e && e[0] == '1'; }();
-  static const bool push_env = [] { const char* e = getenv("B200KV_PUSH"); return !(e && e[0] == '0'); }();
+  static const bool push_env = [] { const char* e = getenv("B200KV_PUSH"); return e && e[0] == '1'; }();
   const bool staged = staged_env;
-  // Reduce-scatter half: PUSH (default) — every rank first stores the slices of its bucket into
-  // their owners' staging areas (NVLink writes only), then the owner sums W local copies; or PULL —
-  // the owner loads its shard of every peer's bucket directly inside the fused kernel.
+  // Reduce-scatter half: PULL (default) — the owner loads its shard of every peer's bucket directly
+  // inside the fused kernel; or PUSH (B200KV_PUSH=1) — every rank first stores the slices of its
+  // bucket into their owners' staging areas (NVLink writes only), then the owner sums W local copies.
+  // Measured equal at 8 GPUs for SGD (0.327 vs 0.325 ms) and slower for LAMB (extra local pass).
   const bool push_rs = push_env && !staged;
   // gradient copy k of the element at flat offset `off`, as seen by the shard owner
   auto grad_src = [&](int k, int64_t off) -> const char* {

@@ -121,7 +121,9 @@ int b200kv_broadcast(b200kv_handle h, int vnum, const int* vkeys, DLManagedTenso
  * (c_api.h:2985-3020; kvstore_local.h:259-267; python/mxnet/optimizer/optimizer.py:2070-2127).
  * The host side keeps the Optimizer's scheduler / multiplier logic and ships resolved scalars,
  * exactly the attributes that reach multi_sgd_mom_update / adam_update / multi_lamb_update. */
-enum { B200KV_OPT_NONE = 0, B200KV_OPT_SGD = 1, B200KV_OPT_ADAM = 2, B200KV_OPT_LAMB = 3 };
+enum { B200KV_OPT_NONE = 0, B200KV_OPT_SGD = 1, B200KV_OPT_ADAM = 2, B200KV_OPT_LAMB = 3,
+       B200KV_OPT_ADAGRAD = 4 /* AdaGrad (python/mxnet/optimizer/optimizer.py:1633-1687; sparse rows:
+                                 _sparse_adagrad_update, optimizer_op-inl.h:2457-2657); epsilon = eps */ };
 typedef struct {
   int32_t kind;             /* B200KV_OPT_* */
   int32_t multi_precision;  /* fp16 weights keep an fp32 master copy (optimizer.py:252-304,583-600) */

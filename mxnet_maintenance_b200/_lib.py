@@ -24,7 +24,7 @@ class OptimizerDesc(C.Structure):
                 ("clip_global_norm", C.c_float)]
 
 
-OPT_NONE, OPT_SGD, OPT_ADAM, OPT_LAMB = 0, 1, 2, 3
+OPT_NONE, OPT_SGD, OPT_ADAM, OPT_LAMB, OPT_ADAGRAD = 0, 1, 2, 3, 4
 
 _VP, _I, _F, _I64 = C.c_void_p, C.c_int, C.c_float, C.c_int64
 _PI = C.POINTER(C.c_int)

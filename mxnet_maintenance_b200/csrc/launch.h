@@ -29,6 +29,7 @@ struct OptScalars {
 // Update kernels: W section is the fp32 weight (dtype kF32) or the fp32 master (dtype kF16).
 int launch_sgd(const MtaCall& c, bool has_mom, const OptScalars& s, const float* gscale);
 int launch_adam(const MtaCall& c, const OptScalars& s, const float* gscale);
+int launch_adagrad(const MtaCall& c, const OptScalars& s, const float* gscale);
 int launch_adamw(const MtaCall& c, const OptScalars& s, const float* rescale_dev);
 // partials [nchunks]: number of non-finite values per chunk
 int launch_nonfinite(const MtaCall& c, float* partials);

@@ -274,6 +274,24 @@ static __global__ void all_finite_final_kernel(const float* __restrict__ sums, i
   }
 }
 
+// AdaGrad, dense branch of AdaGrad.update (python/mxnet/optimizer/optimizer.py:1681-1687), the same
+// chain of fp32 operations the NDArray expressions perform:
+//   g = g*rescale; clip; history += g*g; div = g / sqrt(history + eps); w += (div + w*wd) * -lr
+struct AdagradOp {
+  static constexpr OpFlags F = {true, true, true, true, true, true, false, false, 0};
+  float eps, rescale, clip;
+  struct PT { float neg_lr, wd; };
+  __device__ __forceinline__ PT prep(float lr, float wd, float, float) const { return {-lr, wd}; }
+  template <typename T>
+  __device__ __forceinline__ void elem(const PT& p, float& w, float g, float& h, float&, float*) const {
+    float gr = __fmul_rn(g, rescale);
+    if (clip >= 0.f) gr = clipf(gr, clip);
+    h = __fadd_rn(h, __fmul_rn(gr, gr));
+    const float div = __fdiv_rn(gr, __fsqrt_rn(__fadd_rn(h, eps)));
+    w = __fadd_rn(w, __fmul_rn(__fadd_rn(div, __fmul_rn(w, p.wd)), p.neg_lr));
+  }
+};
+
 // LAMB update direction u = m_hat/(sqrt(v_hat)+eps) + wd*w   (multi_lamb.cc:56-72)
 // aux0 = 1 - beta1^t, aux1 = 1 - beta2^t (computed with the host's powf, as the CPU kernel does)
 __device__ __forceinline__ float lamb_dir(float m, float v, float w, float wd, float c1, float c2,

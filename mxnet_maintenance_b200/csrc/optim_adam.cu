@@ -12,6 +12,11 @@ int launch_adam(const MtaCall& c, const OptScalars& s, const float* gscale) {
   return launch_update(c, op, gscale, nullptr);
 }
 
+int launch_adagrad(const MtaCall& c, const OptScalars& s, const float* gscale) {
+  AdagradOp op{s.eps, s.rescale, s.clip};
+  return launch_update(c, op, gscale, nullptr);
+}
+
 int launch_adamw(const MtaCall& c, const OptScalars& s, const float* rescale_dev) {
   AdamWOp op{s.beta1, s.beta2, s.eps, s.clip, rescale_dev};
   return launch_update(c, op, nullptr, nullptr);

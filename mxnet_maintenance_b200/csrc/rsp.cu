@@ -251,10 +251,12 @@ void Store::push_rsp(int key, int ncopies, DLManagedTensor* const* idx, DLManage
     k.merged_valid = true;
   } else {
     KV_CHECK(k.full, "lazy row update needs the dense table (the key was overwritten by an updater-less push)");
-    KV_CHECK(opt_.kind == B200KV_OPT_SGD || opt_.kind == B200KV_OPT_ADAM,
-             "row-sparse keys support lazy SGD(-momentum) and Adam updates");
+    KV_CHECK(opt_.kind == B200KV_OPT_SGD || opt_.kind == B200KV_OPT_ADAM || opt_.kind == B200KV_OPT_ADAGRAD,
+             "row-sparse keys support lazy SGD(-momentum), Adam and AdaGrad updates");
+    // the sparse AdaGrad op only exists for wd == 0 (AdagradStorageType, optimizer_op-inl.h:2497-2502)
+    KV_CHECK(opt_.kind != B200KV_OPT_ADAGRAD || k.wd == 0.f, "sparse AdaGrad requires wd == 0");
     const size_t bytes = static_cast<size_t>(k.num_rows) * k.row_len * 4;
-    const bool want_s0 = opt_.kind == B200KV_OPT_ADAM || opt_.momentum != 0.f;
+    const bool want_s0 = opt_.kind == B200KV_OPT_ADAM || opt_.kind == B200KV_OPT_ADAGRAD || opt_.momentum != 0.f;
     if (want_s0 && !k.has_s0) {
       k.s0.reserve(bytes);
       CUDA_OK(cudaMemsetAsync(k.s0.p, 0, bytes, stream_));
@@ -276,7 +278,9 @@ void Store::push_rsp(int key, int ncopies, DLManagedTensor* const* idx, DLManage
     else rsp_reduce_kernel<MODE, false><<<grid, 128, 0, stream_>>>(                                      \
         in, pay, k.seg_start.as<int32_t>(), k.uniq.as<int64_t>(), k.count.as<int64_t>(), k.row_len, nullptr, up); \
   } while (0)
-    if (opt_.kind == B200KV_OPT_SGD) GO(kRspSgd); else GO(kRspAdam);
+    if (opt_.kind == B200KV_OPT_SGD) GO(kRspSgd);
+    else if (opt_.kind == B200KV_OPT_ADAM) GO(kRspAdam);
+    else GO(kRspAdagrad);
 #undef GO
     ++launches_;
   }

@@ -259,7 +259,7 @@ head_write_kernel(const uint32_t* __restrict__ keys, int n, const uint32_t* __re
 }
 
 // ---- segmented row reduce (+ optional lazy update) ---------------------------------------------------
-enum RspMode { kRspStore = 0, kRspSgd = 1, kRspAdam = 2 };
+enum RspMode { kRspStore = 0, kRspSgd = 1, kRspAdam = 2, kRspAdagrad = 3 };
 
 struct RspUpdate {
   int mode;
@@ -321,6 +321,14 @@ rsp_reduce_kernel(const RspInputs in, const uint32_t* __restrict__ pay, const in
             mom = __fsub_rn(__fsub_rn(a, bb), cc);
             if (up.has_mom) up.s0[o + j] = mom;
             up.table[o + j] = __fadd_rn(w, mom);
+          } else if (MODE == kRspAdagrad) {
+            // AdagradDnsRspDnsKernel (optimizer_op-inl.h:2514-2539): h += g'^2; w -= g'/sqrt(h+eps) * lr
+            float gr = __fmul_rn(acc[j], up.rescale);
+            if (up.clip >= 0.f) gr = clipf(gr, up.clip);
+            const float h = __fadd_rn(up.s0[o + j], __fmul_rn(gr, gr));
+            up.s0[o + j] = h;
+            const float div = __fdiv_rn(gr, __fsqrt_rn(__fadd_rn(h, up.eps)));
+            up.table[o + j] = __fsub_rn(w, __fmul_rn(div, up.lr));
           } else {
             // AdamDnsRspDnsKernel<cpu>: note (1-beta2)*square(clip(g)) with clipping but
             // (1-beta2)*g*g (left to right) without

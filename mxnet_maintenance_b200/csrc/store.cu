@@ -214,7 +214,7 @@ void Store::seal() {
 // ---- optimizer -----------------------------------------------------------------------------------
 void Store::set_optimizer(const b200kv_optimizer& o) {
   use_device();
-  KV_CHECK(o.kind >= B200KV_OPT_NONE && o.kind <= B200KV_OPT_LAMB, "unknown optimizer kind " << o.kind);
+  KV_CHECK(o.kind >= B200KV_OPT_NONE && o.kind <= B200KV_OPT_ADAGRAD, "unknown optimizer kind " << o.kind);
   const bool had_mom = opt_.kind == B200KV_OPT_SGD && opt_.momentum != 0.f;
   const bool has_mom = o.kind == B200KV_OPT_SGD && o.momentum != 0.f;
   const bool reset = o.kind != opt_.kind || o.multi_precision != opt_.multi_precision || had_mom != has_mom;
@@ -255,7 +255,8 @@ void Store::set_hyper(int num, const int* keys, const float* lrs, const float* w
 // (python/mxnet/optimizer/optimizer.py:2096-2098); they cover only this rank's shard when world > 1.
 void Store::ensure_states(Segment& s) {
   const bool want_s0 = (opt_.kind == B200KV_OPT_SGD && opt_.momentum != 0.f) ||
-                       opt_.kind == B200KV_OPT_ADAM || opt_.kind == B200KV_OPT_LAMB;
+                       opt_.kind == B200KV_OPT_ADAM || opt_.kind == B200KV_OPT_LAMB ||
+                       opt_.kind == B200KV_OPT_ADAGRAD;
   const bool want_s1 = opt_.kind == B200KV_OPT_ADAM || opt_.kind == B200KV_OPT_LAMB;
   const bool want_master = use_mp(s);
   if (s.state_len == 0) {
@@ -356,6 +357,9 @@ void Store::update_chunks(DensePlan& p, const ChunkPlan& cp, const MtaCall& call
       break;
     case B200KV_OPT_ADAM:
       launches_ += launch_adam(c, sc_, gscale);
+      break;
+    case B200KV_OPT_ADAGRAD:
+      launches_ += launch_adagrad(c, sc_, gscale);
       break;
     case B200KV_OPT_LAMB: {
       float* partials = p.partials.as<float>();

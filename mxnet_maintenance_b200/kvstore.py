@@ -280,6 +280,9 @@ class B200(KVStoreBase):
             elif kind == "adam":
                 desc = (_lib.OPT_ADAM, int(bool(o.multi_precision)), 0, 0.0, o.beta1, o.beta2,
                         o.epsilon, o.rescale_grad, clip, -1.0, -1.0, gclip)
+            elif kind == "adagrad":
+                desc = (_lib.OPT_ADAGRAD, int(bool(o.multi_precision)), 0, 0.0, 0.0, 0.0,
+                        o.float_stable_eps, o.rescale_grad, clip, -1.0, -1.0, gclip)
             else:
                 desc = (_lib.OPT_LAMB, int(bool(o.multi_precision)), int(bool(o.bias_correction)), 0.0,
                         o.beta1, o.beta2, o.epsilon, o.rescale_grad, clip,
@@ -661,6 +664,8 @@ class B200(KVStoreBase):
                 continue
             if kind == "sgd":
                 st = s0 if w32 is None else (s0, w32)
+            elif kind == "adagrad":
+                st = s0 if w32 is None else (w32, s0)
             else:
                 st = (s0, s1) if w32 is None else (w32, (s0, s1))
             states[key] = st
@@ -690,6 +695,8 @@ class B200(KVStoreBase):
         for key, st in self._updater.states.items():
             if kind == "sgd":
                 s0, s1, w32 = (st[0], None, st[1]) if isinstance(st, tuple) else (st, None, None)
+            elif kind == "adagrad":
+                s0, s1, w32 = (st[1], None, st[0]) if isinstance(st, tuple) else (st, None, None)
             elif isinstance(st[1], tuple):
                 w32, (s0, s1) = st
             else:

@@ -11,7 +11,7 @@ math: every update runs in the CUDA library.
 import math
 import pickle
 
-__all__ = ["Optimizer", "SGD", "Adam", "LAMB", "create", "Updater", "resolve_step"]
+__all__ = ["Optimizer", "SGD", "Adam", "LAMB", "AdaGrad", "create", "Updater", "resolve_step"]
 
 
 class Optimizer(object):
@@ -139,6 +139,15 @@ class LAMB(Optimizer):
         self.aggregate_num = 45
 
 
+@Optimizer.register
+class AdaGrad(Optimizer):
+    """optimizer.py:1633-1687 (``eps`` is the history stabiliser ``float_stable_eps``)."""
+
+    def __init__(self, eps=1e-7, **kwargs):
+        super(AdaGrad, self).__init__(**kwargs)
+        self.float_stable_eps = eps
+
+
 def create(name, **kwargs):
     """mx.optimizer.create (optimizer.py:169-199)."""
     if isinstance(name, Optimizer):
@@ -150,9 +159,9 @@ def kind_of(optimizer):
     """'sgd' | 'adam' | 'lamb' for any object that looks like the reference classes."""
     for klass in type(optimizer).__mro__:
         n = klass.__name__.lower()
-        if n in ("sgd", "adam", "lamb"):
+        if n in ("sgd", "adam", "lamb", "adagrad"):
             return n
-    raise ValueError("the b200 kvstore runs SGD, Adam and LAMB on the store; got %s (use "
+    raise ValueError("the b200 kvstore runs SGD, Adam, LAMB and AdaGrad on the store; got %s (use "
                      "update_on_kvstore=False for other optimizers)" % type(optimizer).__name__)
 
 

@@ -355,6 +355,25 @@ int mxref_adam_rsp(int64_t nnr, int64_t row_len, float* out, float* mean, float*
   return 0;
 }
 
+/* AdagradDnsRspDnsKernel<cpu>::Map, optimizer_op-inl.h:2514-2539 (lazy rows, wd must be 0) */
+int mxref_adagrad_rsp(int64_t nnr, int64_t row_len, float* out, float* hist, const float* w,
+                      const int64_t* idx, const float* g, float clip, float eps, float lr, float rescale,
+                      int nthread) {
+#pragma omp parallel for num_threads(nthread)
+  for (int64_t i = 0; i < nnr; ++i) {
+    for (int64_t j = 0; j < row_len; ++j) {
+      int64_t di = idx[i] * row_len + j, gi = i * row_len + j;
+      float gr = g[gi] * rescale;
+      if (clip >= 0.0f) gr = clipf(gr, clip);
+      const float sq = gr * gr;
+      hist[di] += sq;
+      const float div = gr / sqrtf(hist[di] + eps);
+      out[di] = w[di] - div * lr;
+    }
+  }
+  return 0;
+}
+
 /* SparseRetainRspThreadKernel::Map, src/operator/tensor/sparse_retain-inl.h:121-150:
  * out_idx[i] = ids[i] always; row copied when present in the source, else left as the caller's zeros. */
 int mxref_sparse_retain(int64_t nids, float* out_data, int64_t* out_idx, const float* in_data,

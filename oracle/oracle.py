@@ -91,6 +91,7 @@ class Oracle:
         L.mxref_multi_sum_sq.argtypes = [C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int]
         L.mxref_sgd_mom_rsp.argtypes = [C.c_int64, C.c_int64] + [C.c_void_p] * 5 + [fp] * 5 + [C.c_int]
         L.mxref_adam_rsp.argtypes = [C.c_int64, C.c_int64] + [C.c_void_p] * 6 + [fp] * 7 + [C.c_int]
+        L.mxref_adagrad_rsp.argtypes = [C.c_int64, C.c_int64] + [C.c_void_p] * 5 + [fp] * 4 + [C.c_int]
         L.mxref_sparse_retain.argtypes = [C.c_int64] + [C.c_void_p] * 5 + [C.c_int64, C.c_int64]
         L.mxref_f32_to_f16.argtypes = [C.c_int64, C.c_void_p, C.c_void_p]
         L.mxref_f32_to_f16.restype = None
@@ -220,6 +221,25 @@ class Oracle:
                                 w.ctypes.data, idx.ctypes.data, g.ctypes.data, clip, beta1, beta2, lr,
                                 wd, eps, rescale, self.nthread)
 
+    def adagrad_rsp(self, w, hist, idx, g, lr, eps=1e-7, rescale=1.0, clip=-1.0):
+        """_sparse_adagrad_update on the rows `idx` (optimizer_op-inl.h:2514-2539)."""
+        row_len = w.shape[1]
+        self.lib.mxref_adagrad_rsp(len(idx), row_len, w.ctypes.data, hist.ctypes.data, w.ctypes.data,
+                                   idx.ctypes.data, g.ctypes.data, clip, eps, lr, rescale, self.nthread)
+
+    @staticmethod
+    def adagrad_dense(w, hist, g, lr, wd, eps=1e-7, rescale=1.0, clip=None):
+        """AdaGrad.update dense branch, a chain of fp32 NDArray ops (optimizer.py:1681-1687):
+        grad = grad*rescale; clip; history += square(grad); div = grad/sqrt(history+eps);
+        weight += (div + weight*wd) * -lr."""
+        f = np.float32
+        gr = g * f(rescale)
+        if clip is not None:
+            gr = np.clip(gr, f(-clip), f(clip))
+        hist += gr * gr
+        div = gr / np.sqrt(hist + f(eps))
+        w += (div + w * f(wd)) * f(-lr)
+
     def sparse_retain(self, src_idx, src_vals, ids):
         """Rows `ids` (int64, sorted unique) of the row-sparse (src_idx, src_vals); absent rows = 0."""
         ids = _i64(ids)
@@ -344,5 +364,16 @@ class LocalStoreModel:
             o.multi_lamb([flat_w], [flat_g], [mean], [var], None if w32 is None else [w32], [lr], [wd],
                          [t], b1, b2, eps, rescale, clip, op.get("lower", -1.0), op.get("upper", -1.0),
                          op.get("bias_correction", True))
+        elif kind == "adagrad":
+            eps = op.get("eps", 1e-7)
+            if key not in self.state:
+                self.state[key] = (flat_w.astype(np.float32) if mp else None, np.zeros(w.size, np.float32))
+            w32, hist = self.state[key]
+            c = clip if clip >= 0 else None
+            if mp:   # Optimizer.update_multi_precision wrapper (optimizer.py:298-304)
+                Oracle.adagrad_dense(w32, hist, flat_g.astype(np.float32), lr, wd, eps, rescale, c)
+                o.f32_to_f16(w32, flat_w)
+            else:
+                Oracle.adagrad_dense(flat_w, hist, flat_g, lr, wd, eps, rescale, c)
         else:
             raise ValueError(kind)

@@ -17,6 +17,7 @@
 //   SparseRetainRspThreadKernel src/operator/tensor/sparse_retain-inl.h:121-150
 //   MultiMPAdamWKernel        src/operator/contrib/adamw-inl.h:346-377
 //   MultiLARSKernel           src/operator/contrib/multi_lars-inl.h:60-72
+//   AdagradDnsRspDnsKernel<cpu> src/operator/optimizer_op-inl.h:2514-2539
 //   mshadow half_t / Tensor<cpu,1,DType> expressions for the CommCPU reduce
 //                             (restated driver: src/kvstore/comm.h:357-410)
 #include <cstdint>
@@ -357,6 +358,16 @@ int mxref_adam_rsp(int64_t nnr, int64_t row_len, float* out, float* mean, float*
   for (int64_t i = 0; i < nnr; ++i)
     AdamDnsRspDnsKernel<kWriteTo, cpu>::Map<float, int64_t>(i, row_len, out, mean, var, w, idx, g,
                                                           clip, beta1, beta2, lr, wd, eps, rescale);
+  return 0;
+}
+
+// _sparse_adagrad_update, lazy rows (optimizer_op-inl.h:2514-2539; requires wd == 0, :2497-2502)
+int mxref_adagrad_rsp(int64_t nnr, int64_t row_len, float* out, float* hist, const float* w,
+                      const int64_t* idx, const float* g, float clip, float eps, float lr, float rescale,
+                      int nthread) {
+#pragma omp parallel for num_threads(nthread)
+  for (int64_t i = 0; i < nnr; ++i)
+    AdagradDnsRspDnsKernel<cpu>::Map<float, int64_t>(i, row_len, out, hist, w, idx, g, clip, eps, lr, rescale);
   return 0;
 }
 

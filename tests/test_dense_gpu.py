@@ -47,6 +47,9 @@ def _run(oracle, shape_name, opt_kind, ncopies, steps=3, mp=False, clip=None, gc
     elif opt_kind == "lamb":
         opt = mb.optimizer.LAMB(**common)
         odict.update(kind="lamb")
+    elif opt_kind == "adagrad":
+        opt = mb.optimizer.AdaGrad(eps=1e-7, **common)
+        odict.update(kind="adagrad", eps=1e-7)
     else:
         opt = None
         odict = None
@@ -416,3 +419,11 @@ def test_bert_large_lamb_clip_full_size(oracle):
         worst_cpu = max(worst_cpu, float(np.abs(wr[k] - truth).max()))
     # the GPU path is closer to the exact-norm result than the CPU reference on every big tensor
     assert worst_gpu < 1e-6 and worst_gpu < worst_cpu
+
+
+@pytest.mark.parametrize("mp", [False, True])
+@pytest.mark.parametrize("clip", [None, 0.0005])
+def test_adagrad_bit_exact(oracle, mp, clip):
+    """AdaGrad on the store (dense branch of AdaGrad.update, optimizer.py:1681-1687)."""
+    _, _, res = _run(oracle, "ragged", "adagrad", 2, mp=mp, clip=clip, wd=0.01)
+    _assert_bits(res)

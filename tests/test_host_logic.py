@@ -84,10 +84,12 @@ def test_adam_bias_correction_folded_into_lr():
 def test_kind_of_and_unsupported():
     assert opt.kind_of(opt.LAMB()) == "lamb"
 
-    class AdaGrad(opt.Optimizer):
+    assert opt.kind_of(opt.AdaGrad()) == "adagrad"
+
+    class RMSProp(opt.Optimizer):
         pass
     with pytest.raises(ValueError):
-        opt.kind_of(AdaGrad())
+        opt.kind_of(RMSProp())
 
 
 def test_shape_lists_match_baseline_configs():

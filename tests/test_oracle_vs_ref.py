@@ -127,7 +127,10 @@ def test_row_sparse_kernels(oracle, oracle_ref):
         me, va = np.zeros_like(W), np.zeros_like(W)
         o.adam_rsp(ww, me, va, idx, gg, 1e-3, 0.01)
         o.adam_rsp(ww, me, va, idx, gg, 1e-3, 0.01, clip=0.2)
-        return np.concatenate([ww.ravel(), mm.ravel(), me.ravel(), va.ravel()])
+        hh = np.zeros_like(W)
+        o.adagrad_rsp(ww, hh, idx, gg, 0.1)
+        o.adagrad_rsp(ww, hh, idx, gg, 0.1, rescale=0.5, clip=0.2)
+        return np.concatenate([ww.ravel(), mm.ravel(), me.ravel(), va.ravel(), hh.ravel()])
     a, b = _both(oracle, oracle_ref, f)
     assert a.tobytes() == b.tobytes()
     ra = oracle.sparse_retain(idx, gg, [0, 1, 7, 29, 30, 49])

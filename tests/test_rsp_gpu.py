@@ -91,7 +91,7 @@ def test_large_row_id(oracle):
     assert pi.tolist() == [3, 793470] and (pv[1] == 7.0).all() and (pv[0] == 0).all()
 
 
-@pytest.mark.parametrize("kind", ["sgd", "sgd_nomom", "adam", "sgd_clip", "adam_clip"])
+@pytest.mark.parametrize("kind", ["sgd", "sgd_nomom", "adam", "sgd_clip", "adam_clip", "adagrad", "adagrad_clip"])
 def test_lazy_row_update(oracle, kind):
     import mxnet_maintenance_b200 as mb0
     rng = np.random.default_rng(11)
@@ -101,6 +101,8 @@ def test_lazy_row_update(oracle, kind):
     if kind.startswith("sgd"):
         mom = 0.0 if "nomom" in kind else 0.9
         opt = mb0.optimizer.SGD(learning_rate=0.1, momentum=mom, wd=1e-3, rescale_grad=0.5, clip_gradient=clip)
+    elif kind.startswith("adagrad"):
+        opt = mb0.optimizer.AdaGrad(learning_rate=0.05, eps=1e-7, rescale_grad=0.5, clip_gradient=clip)
     else:
         opt = mb0.optimizer.Adam(learning_rate=1e-3, wd=0.01, rescale_grad=0.5, clip_gradient=clip)
     kv, mb = _kv(table, opt)
@@ -113,6 +115,8 @@ def test_lazy_row_update(oracle, kind):
         midx, mval = oracle.rsp_sum(grads)
         if kind.startswith("sgd"):
             oracle.sgd_mom_rsp(ref, s0, midx, mval, 0.1, 1e-3, mom, 0.5, clip if clip else -1.0)
+        elif kind.startswith("adagrad"):
+            oracle.adagrad_rsp(ref, s0, midx, mval, 0.05, 1e-7, 0.5, clip if clip else -1.0)
         else:
             oracle.adam_rsp(ref, s0, s1, midx, mval, adam_lr(1e-3, 0.9, 0.999, step + 1), 0.01, rescale=0.5,
                             clip=clip if clip else -1.0)

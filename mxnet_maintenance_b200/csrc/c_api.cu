@@ -446,6 +446,7 @@ int b200kv_preloaded_multi_sgd_update(int num, int dtype, void* const* weights, 
   MtaCall c = make_call(w, num, dtype, weights, grads, moms, nullptr, weights32, nullptr, nullptr, nullptr,
                         nullptr, st, dev);
   launch_fill_lrwd(c, lrs_dev, wds_dev);
+  w.ring.invalidate();   // the uploaded table was patched on the device
   OptScalars s;
   s.momentum = momentum; s.rescale = rescale_grad; s.clip = clip_gradient;
   launch_sgd(c, moms != nullptr, s, nullptr);

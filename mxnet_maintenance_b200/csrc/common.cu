@@ -54,6 +54,7 @@ TableRing::~TableRing() {
 
 uint64_t* TableRing::begin(size_t bytes) {
   cur_ = (cur_ + 1) % kSlots;
+  if (cur_ == last_) cur_ = (cur_ + 1) % kSlots;   // never stage over the table that may be reused
   Slot& s = slots_[cur_];
   if (s.busy) {  // the launches that read this slot's previous table must have finished
     CUDA_OK(cudaEventSynchronize(s.done));
@@ -75,14 +76,25 @@ uint64_t* TableRing::begin(size_t bytes) {
 
 const uint64_t* TableRing::commit(cudaStream_t stream) {
   Slot& s = slots_[cur_];
+  reused_ = last_ >= 0 && last_bytes_ == cur_bytes_ &&
+            std::memcmp(slots_[last_].host, s.host, cur_bytes_) == 0;
+  if (reused_) {
+    cur_ = cur_ == 0 ? kSlots - 1 : cur_ - 1;   // hand the untouched staging slot back
+    if (cur_ == last_) cur_ = cur_ == 0 ? kSlots - 1 : cur_ - 1;
+    return static_cast<const uint64_t*>(slots_[last_].dev);
+  }
   CUDA_OK(cudaMemcpyAsync(s.dev, s.host, cur_bytes_, cudaMemcpyHostToDevice, stream));
+  last_ = cur_;
+  last_bytes_ = cur_bytes_;
   return static_cast<const uint64_t*>(s.dev);
 }
 
 void TableRing::end(cudaStream_t stream) {
-  Slot& s = slots_[cur_];
+  // the event guards the device table these launches read: the reused one, or the new upload
+  Slot& s = slots_[last_ >= 0 && reused_ ? last_ : cur_];
   CUDA_OK(cudaEventRecord(s.done, stream));
   s.busy = true;
+  reused_ = false;
 }
 
 // ---- ChunkPlan ---------------------------------------------------------------------------------

@@ -90,6 +90,8 @@ class TableRing {
   const uint64_t* commit(cudaStream_t stream);
   // call after the launches that read the committed table have been enqueued
   void end(cudaStream_t stream);
+  // the device copy of the last table was modified in place: never reuse it
+  void invalidate() { last_ = -1; }
 
  private:
   struct Slot {
@@ -102,6 +104,12 @@ class TableRing {
   Slot slots_[kSlots];
   int cur_ = -1;
   size_t cur_bytes_ = 0;
+  // the slot whose device table was uploaded last: a call whose table is byte-identical (same
+  // arrays, same scalars — the steady state of SGD with a constant learning rate) reuses it and
+  // skips the upload, so consecutive steps are back-to-back kernel launches
+  int last_ = -1;
+  size_t last_bytes_ = 0;
+  bool reused_ = false;
 };
 
 // A chunk list + per-tensor chunk ranges resident on the device

@@ -18,7 +18,7 @@ import os
 
 from . import _lib
 from ._lib import B200KVError, OptimizerDesc, check_call
-from .base import KVStoreBase
+from .base import KVStoreBase, HAVE_MXNET
 from .dlpack import HandleCache
 from . import optimizer as opt_mod
 
@@ -670,6 +670,14 @@ class B200(KVStoreBase):
                 st = (s0, s1) if w32 is None else (w32, (s0, s1))
             states[key] = st
         self.wait()
+        if HAVE_MXNET:   # pragma: no cover - files interchangeable with native stores hold NDArrays
+            import mxnet as mx
+
+            def _nd(x):
+                if isinstance(x, tuple):
+                    return tuple(_nd(y) for y in x)
+                return None if x is None else mx.nd.array(x, dtype=x.dtype)
+            states = {k: _nd(v) for k, v in states.items()}
         self._updater.states = states
         return states
 
@@ -705,7 +713,8 @@ class B200(KVStoreBase):
             for which, arr in ((2, w32), (0, s0), (1, s1)):
                 if arr is None:
                     continue
-                t = _from_numpy(_np.ascontiguousarray(_np.asarray(arr, dtype=_np.float32).reshape(-1)), self._device)
+                host = arr.asnumpy() if hasattr(arr, "asnumpy") else _np.asarray(arr)   # NDArray or numpy
+                t = _from_numpy(_np.ascontiguousarray(host.astype(_np.float32).reshape(-1)), self._device)
                 p, keep = self._handles([t], False)
                 check_call(self._lib.b200kv_set_state(self._h, ck[0], which, p[0]))
         self.wait()

@@ -41,8 +41,11 @@ int launch_multi_lars(int n, const float* lrs, const float* w2, const float* g2,
 // overwrite the (lr, wd) section of an uploaded table from device arrays
 int launch_fill_lrwd(const MtaCall& c, const float* lrs_dev, const float* wds_dev);
 // partials: [nchunks][2] floats
-int launch_lamb1(const MtaCall& c, const OptScalars& s, const float* gscale, float* partials);
+// store_u: pass 1 also writes the update direction u to the X section, and pass 2 (launch_lamb2u)
+// reads it back instead of recomputing it from m, v, w
+int launch_lamb1(const MtaCall& c, const OptScalars& s, const float* gscale, float* partials, bool store_u = false);
 int launch_lamb2(const MtaCall& c, const OptScalars& s, const float* ratio);
+int launch_lamb2u(const MtaCall& c, const float* ratio);
 // partials: [nchunks] floats; squares of the G section (ngrad copies summed first)
 int launch_sumsq(const MtaCall& c, float* partials);
 // W section <- sum of the G copies; optionally also to the out copies.  The W section holds

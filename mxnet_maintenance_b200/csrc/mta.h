@@ -22,7 +22,7 @@ struct Chunk {          // 16 bytes
 };
 
 // The table is one blob of 8-byte words laid out as consecutive sections of `nt` words each:
-//   grad[0..ngrad) | out[0..nout) | w | s0 | s1 | size | (lr,wd) | (aux0,aux1)
+//   grad[0..ngrad) | out[0..nout) | w | s0 | s1 | x | (lr,wd) | (aux0,aux1)
 // Pointers are per-tensor element-0 addresses; a section may hold nulls when unused.
 // Cross-GPU flag blocks of the peer-memory path (see optim.cuh): flags[k] is rank k's block
 // [ready[8] | done[8] | error | cta counter] as mapped into this process.
@@ -51,6 +51,7 @@ inline size_t mta_blob_words(int nt, int ngrad, int nout) {
   return static_cast<size_t>(nt) * static_cast<size_t>(ngrad + nout + 6);
 }
 
-enum Section { kSecW = 0, kSecS0 = 1, kSecS1 = 2, kSecSize = 3, kSecLrWd = 4, kSecAux = 5 };
+// kSecX: optional fp32 scratch array per tensor (LAMB keeps its update direction there between passes)
+enum Section { kSecW = 0, kSecS0 = 1, kSecS1 = 2, kSecX = 3, kSecLrWd = 4, kSecAux = 5 };
 
 }  // namespace b200kv

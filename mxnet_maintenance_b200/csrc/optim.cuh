@@ -142,7 +142,11 @@ __device__ __forceinline__ float grad1(const MtaArgs& a, int t, int64_t e) {
 struct OpFlags {
   bool read_g, read_w, write_w, write_out, read_s0, write_s0, read_s1, write_s1;
   int nred;
+  // optional fp32 scratch array X (table section kSecX): the element is handed to / taken from
+  // elem() through red[kXSlot]
+  bool read_x = false, write_x = false;
 };
+constexpr int kXSlot = 2;
 
 // multi_sgd_update / multi_sgd_mom_update / multi_mp_sgd(_mom)_update
 template <bool HAS_MOM>
@@ -307,8 +311,9 @@ __device__ __forceinline__ float lamb_dir(float m, float v, float w, float wd, f
 // pass 1: moments, and per-chunk partial sums of w^2 (in the weight dtype, multi_lamb-inl.h:286-289)
 // and u^2.  u is not stored: pass 2 recomputes it from the new m, v and the unchanged w, which
 // costs the same HBM bytes as writing and re-reading a temp_g buffer but no scratch memory.
+template <bool STORE_U>
 struct Lamb1Op {
-  static constexpr OpFlags F = {true, true, false, false, true, true, true, true, 2};
+  static constexpr OpFlags F = {true, true, false, false, true, true, true, true, 2, false, STORE_U};
   float beta1, beta2, eps, rescale, clip;
   int bias_correction;
   struct PT { float wd, c1, c2, omb1, omb2; };
@@ -326,6 +331,7 @@ struct Lamb1Op {
     const float wt = round_to<T>(w);
     red[0] = __fadd_rn(red[0], round_to<T>(__fmul_rn(wt, wt)));
     red[1] = __fadd_rn(red[1], __fmul_rn(u, u));
+    if (STORE_U) red[kXSlot] = u;   // kept for pass 2 (the reference's temp_g, multi_lamb.cc:77)
   }
 };
 
@@ -345,6 +351,20 @@ struct Lamb2Op {
                                        float*) const {
     const float u = lamb_dir(m, v, w, p.wd, p.c1, p.c2, eps, bias_correction != 0);
     w = __fsub_rn(w, __fmul_rn(p.lr_adj, u));
+  }
+};
+
+// pass 2 when pass 1 stored u: w -= lr * ratio * u, a pure stream (reads w, u; writes w)
+struct Lamb2UOp {
+  static constexpr OpFlags F = {false, true, true, true, false, false, false, false, 0, true, false};
+  const float* ratio;
+  struct PT { float lr_adj; };
+  __device__ __forceinline__ PT prep_t(float lr, float, float, float, int t) const {
+    return {__fmul_rn(lr, ratio[t])};
+  }
+  template <typename T>
+  __device__ __forceinline__ void elem(const PT& p, float& w, float, float&, float&, float* red) const {
+    w = __fsub_rn(w, __fmul_rn(p.lr_adj, red[kXSlot]));
   }
 };
 
@@ -433,7 +453,7 @@ mta_kernel(const MtaArgs a, const Op op, const float* __restrict__ gscale,
   const int tid = threadIdx.x;
   const float gs = (F.read_g && gscale != nullptr) ? *gscale : 1.0f;
   const bool use_gs = F.read_g && gscale != nullptr;
-  float red[2] = {0.f, 0.f};
+  float red[3] = {0.f, 0.f, 0.f};
 
   if (a.sync != nullptr && (a.sync_mode & 1)) {
     // every rank's gradient bucket must be complete before this rank reads its shard of it
@@ -452,6 +472,7 @@ mta_kernel(const MtaArgs a, const Op op, const float* __restrict__ gscale,
     WT* const wp = reinterpret_cast<WT*>(sec(a, kSecW)[t]);
     float* const s0p = reinterpret_cast<float*>(sec(a, kSecS0)[t]);
     float* const s1p = reinterpret_cast<float*>(sec(a, kSecS1)[t]);
+    float* const xp = reinterpret_cast<float*>(sec(a, kSecX)[t]);
     const float2 lrwd = *reinterpret_cast<const float2*>(&sec(a, kSecLrWd)[t]);
     const float2 aux = *reinterpret_cast<const float2*>(&sec(a, kSecAux)[t]);
     const typename Op::PT pt = op_prep(op, lrwd.x, lrwd.y, aux.x, aux.y, t);
@@ -464,6 +485,7 @@ mta_kernel(const MtaArgs a, const Op op, const float* __restrict__ gscale,
     if (F.read_w || F.write_w) bits |= (reinterpret_cast<uint64_t>(wp) + oW) * mW;
     if (F.read_s0 || F.write_s0) bits |= reinterpret_cast<uint64_t>(s0p) + o4;
     if (F.read_s1 || F.write_s1) bits |= reinterpret_cast<uint64_t>(s1p) + o4;
+    if (F.read_x || F.write_x) bits |= reinterpret_cast<uint64_t>(xp) + o4;
     constexpr int NGC = NG > 0 ? NG : 1;
     const T* gp[NGC];
     if (F.read_g) {
@@ -479,12 +501,13 @@ mta_kernel(const MtaArgs a, const Op op, const float* __restrict__ gscale,
       const int nvec = ch.len >> 2;
       constexpr int U = Unroll<NG>::value;
       for (int v0 = 0; v0 < nvec; v0 += U * kThreads) {
-      float w[U][4], g[U][4], s0[U][4], s1[U][4];
+      float w[U][4], g[U][4], s0[U][4], s1[U][4], x[U][4];
 #pragma unroll
       for (int u = 0; u < U; ++u) {
         const int v = v0 + u * kThreads + tid;
         if (v < nvec) {
           const int64_t e = base + 4 * v;
+          if (F.read_x) ld4(xp + e, x[u]);
           if (F.read_g) grad4<T, NG>(a, gp, t, e, g[u]);
           if (F.read_w) ld4(wp + e, w[u]);
           if (F.read_s0) ld4(s0p + e, s0[u]);
@@ -499,8 +522,11 @@ mta_kernel(const MtaArgs a, const Op op, const float* __restrict__ gscale,
 #pragma unroll
           for (int j = 0; j < 4; ++j) {
             if (use_gs) g[u][j] = round_to<T>(__fmul_rn(g[u][j], gs));
+            if (F.read_x) red[kXSlot] = x[u][j];
             op.template elem<T>(pt, w[u][j], g[u][j], s0[u][j], s1[u][j], red);
+            if (F.write_x) x[u][j] = red[kXSlot];
           }
+          if (F.write_x) st4(xp + e, x[u]);
           if (F.write_s0) st4(s0p + e, s0[u]);
           if (F.write_s1) st4(s1p + e, s1[u]);
           if (F.write_w) st4(wp + e, w[u]);
@@ -519,7 +545,9 @@ mta_kernel(const MtaArgs a, const Op op, const float* __restrict__ gscale,
       if (F.read_w) w = ld1(wp + e);
       if (F.read_s0) s0 = s0p[e];
       if (F.read_s1) s1 = s1p[e];
+      if (F.read_x) red[kXSlot] = xp[e];
       op.template elem<T>(pt, w, g, s0, s1, red);
+      if (F.write_x) xp[e] = red[kXSlot];
       if (F.write_s0) s0p[e] = s0;
       if (F.write_s1) s1p[e] = s1;
       if (F.write_w) st1(wp + e, w);

@@ -3,9 +3,18 @@
 
 namespace b200kv {
 
-int launch_lamb1(const MtaCall& c, const OptScalars& s, const float* gscale, float* partials) {
-  Lamb1Op op{s.beta1, s.beta2, s.eps, s.rescale, s.clip, s.bias_correction};
+int launch_lamb1(const MtaCall& c, const OptScalars& s, const float* gscale, float* partials, bool store_u) {
+  if (store_u) {
+    Lamb1Op<true> op{s.beta1, s.beta2, s.eps, s.rescale, s.clip, s.bias_correction};
+    return launch_update(c, op, gscale, partials);
+  }
+  Lamb1Op<false> op{s.beta1, s.beta2, s.eps, s.rescale, s.clip, s.bias_correction};
   return launch_update(c, op, gscale, partials);
+}
+
+int launch_lamb2u(const MtaCall& c, const float* ratio) {
+  Lamb2UOp op{ratio};
+  return launch_update(c, op, nullptr, nullptr);
 }
 
 int launch_lamb2(const MtaCall& c, const OptScalars& s, const float* ratio) {

@@ -226,7 +226,7 @@ void Store::set_optimizer(const b200kv_optimizer& o) {
         s.w_stale = false;
       }
       CUDA_OK(cudaStreamSynchronize(stream_));
-      s.master.release(); s.s0.release(); s.s1.release();
+      s.master.release(); s.s0.release(); s.s1.release(); s.xbuf.release();
       s.has_master = s.has_s0 = s.has_s1 = false;
       s.state_len = 0;
     }
@@ -273,6 +273,10 @@ void Store::ensure_states(Segment& s) {
     s.s1.reserve(bytes);
     CUDA_OK(cudaMemsetAsync(s.s1.p, 0, bytes, stream_));
     s.has_s1 = true;
+  }
+  if (opt_.kind == B200KV_OPT_LAMB && s.xbuf.p == nullptr) {
+    static const bool keep_u = [] { const char* e = getenv("B200KV_LAMB_RECOMPUTE"); return !(e && e[0] == '1'); }();
+    if (keep_u) s.xbuf.reserve(bytes);
   }
   if (want_master && !s.has_master) {
     s.master.reserve(bytes);
@@ -368,13 +372,14 @@ void Store::update_chunks(DensePlan& p, const ChunkPlan& cp, const MtaCall& call
       MtaCall c1 = c, c2 = c;
       c1.sync_mode = c.sync_mode & 1;   // pass 1 is the first reader of the (peer) gradients
       c2.sync_mode = c.sync_mode & 2;   // pass 2 is the last writer of the (peer) weights
-      launches_ += launch_lamb1(c1, sc_, gscale, partials);
+      const bool keep_u = segs_[p.seg]->xbuf.p != nullptr;
+      launches_ += launch_lamb1(c1, sc_, gscale, partials, keep_u);
       launches_ += launch_reduce_partials(partials, cp, 2, sums, stream_);
       if (world_ > 1)  // per-tensor norms span shards: one tiny all-reduce between the two passes
         NCCL_OK(NcclApi::get().AllReduce(sums, sums, 2 * static_cast<size_t>(c.nt), ncclFloat32, ncclSum,
                                          reinterpret_cast<ncclComm_t>(comm_), stream_));
       launches_ += launch_lamb_ratio(sums, c.nt, sc_.lower, sc_.upper, ratio, stream_);
-      launches_ += launch_lamb2(c2, sc_, ratio);
+      launches_ += keep_u ? launch_lamb2u(c2, ratio) : launch_lamb2(c2, sc_, ratio);
       break;
     }
     default:
@@ -430,6 +435,7 @@ void Store::run_class(Mode mode, DensePlan& p, const std::vector<const Entry*>& 
       b.S(kSecW, t, mp ? at(s.master, ki.off - s.state_begin, 4) : at(s.wbuf, ki.off, 4));
       if (s.has_s0) b.S(kSecS0, t, at(s.s0, ki.off - s.state_begin, 4));
       if (s.has_s1) b.S(kSecS1, t, at(s.s1, ki.off - s.state_begin, 4));
+      if (s.xbuf.p) b.S(kSecX, t, at(s.xbuf, ki.off - s.state_begin, 4));
       b.F2(kSecLrWd, t, ki.lr, ki.wd);
       if (opt_.kind == B200KV_OPT_LAMB) {
         // 1 - beta^t with the host's powf in fp32, as MultiLAMBKernelStep1 does per element
@@ -746,6 +752,7 @@ void Store::run_class_p2p(DensePlan& p, Segment& s, const std::vector<const Entr
       u.S(kSecW, t, mp ? at(s.master, ki.off - s.state_begin, 4) : at(s.wbuf, ki.off, 4));
       if (s.has_s0) u.S(kSecS0, t, at(s.s0, ki.off - s.state_begin, 4));
       if (s.has_s1) u.S(kSecS1, t, at(s.s1, ki.off - s.state_begin, 4));
+      if (s.xbuf.p) u.S(kSecX, t, at(s.xbuf, ki.off - s.state_begin, 4));
       u.F2(kSecLrWd, t, ki.lr, ki.wd);
       if (opt_.kind == B200KV_OPT_LAMB) {
         const float tf = static_cast<float>(ki.step);

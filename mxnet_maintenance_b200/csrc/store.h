@@ -39,6 +39,7 @@ struct Segment {
   DevBuf gbuf;         // gradient fusion bucket, `dtype`, [total] (world > 1)
   DevBuf master;       // fp32 master weights (multi-precision), [state_len]
   DevBuf s0, s1;       // fp32 optimizer state, [state_len]
+  DevBuf xbuf;         // fp32 scratch, [state_len]: LAMB's update direction between its two passes
   int64_t state_begin = 0, state_len = 0;  // element range the state arrays cover
   bool has_s0 = false, has_s1 = false, has_master = false;
   bool w_stale = false;  // world == 1 && master: wbuf lags behind master (pull casts the master)

@@ -427,3 +427,54 @@ def test_adagrad_bit_exact(oracle, mp, clip):
     """AdaGrad on the store (dense branch of AdaGrad.update, optimizer.py:1681-1687)."""
     _, _, res = _run(oracle, "ragged", "adagrad", 2, mp=mp, clip=clip, wd=0.01)
     _assert_bits(res)
+
+
+@pytest.mark.parametrize("kind", ["sgd", "adam", "lamb", "adamw"])
+@pytest.mark.parametrize("dt", [torch.float32, torch.float16])
+def test_no_out_of_bounds_writes(kind, dt):
+    """compute-sanitizer is unavailable on this pool, so guard every array with canary regions and
+    check that no kernel wrote outside [begin, end) — for odd sizes, odd alignments (arrays that
+    start 4 / 2 bytes past a 16-byte boundary take the scalar path) and chunk-boundary sizes."""
+    from mxnet_maintenance_b200 import ops
+    sizes = [1, 2, 3, 5, 63, 4095, 4096, 4097, 8191, 12289]
+    mp = dt == torch.float16
+    PAD = 64
+
+    def guarded(n, dtype, shift):
+        buf = torch.full((n + 2 * PAD + shift,), 7.0, device="cuda", dtype=dtype)
+        return buf, buf[PAD + shift:PAD + shift + n]
+
+    results = []
+    for shift in (0, 1, 3):
+        gen = torch.Generator(device="cuda").manual_seed(5)     # same values at every alignment
+        bufs, w, g, s0, s1, w32 = [], [], [], [], [], []
+        for n in sizes:
+            for lst, dtype in ((w, dt), (g, dt), (s0, torch.float32), (s1, torch.float32), (w32, torch.float32)):
+                b, v = guarded(n, dtype, shift)
+                v.copy_(torch.rand(n, device="cuda", generator=gen) * 0.01)
+                bufs.append((b, n, shift))
+                lst.append(v)
+        m32 = w32 if mp else None
+        if kind == "sgd":
+            ops.multi_sgd_update(w, g, 0.1, 1e-3, moms=s0, weights32=m32, momentum=0.9)
+        elif kind == "adam":
+            ops.multi_adam_update(w, g, s0, s1, 1e-3, 0.01, weights32=m32)
+        elif kind == "lamb":
+            ops.multi_lamb_update(w, g, s0, s1, 1e-3, 0.01, 1, weights32=m32)
+        else:
+            ops.multi_adamw_update(w, g, s0, s1, torch.ones(1, device="cuda"), 1e-3, 0.01, 1.0, weights32=m32)
+        results.append([x.clone() for x in w + s0 + s1 + w32])
+        ops.clip_global_norm(g, 1e-3)
+        ops.reset_arrays(g)
+        torch.cuda.synchronize()
+        for b, n, sh in bufs:
+            assert (b[:PAD + sh] == 7.0).all() and (b[PAD + sh + n:] == 7.0).all(), (kind, n, sh)
+        assert all((x == 0).all() for x in g)
+    # the scalar (unaligned) path computes the same bits as the 128-bit vector path
+    # (LAMB's norms are summed in a different order on the two paths: tolerance instead of bits)
+    for other in results[1:]:
+        for a, b in zip(results[0], other):
+            if kind == "lamb":
+                assert torch.allclose(a.float(), b.float(), rtol=2e-3 if mp else 1e-5, atol=1e-6)
+            else:
+                assert torch.equal(a, b)

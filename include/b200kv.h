@@ -81,6 +81,19 @@ int b200kv_wait(b200kv_handle h);
 int b200kv_comm_unique_id(char out_id[128]);
 int b200kv_comm_init(b200kv_handle h, const char id[128]);
 
+/* Optional: let the host side allocate the store's exchange buffers (weight segment, gradient
+ * bucket, flag block) as SYMMETRIC memory — the same allocation made by every rank, mapped into
+ * every rank, plus an NVLink-SHARP multicast address (e.g. torch.distributed._symmetric_memory).
+ * With it the fused step uses multimem.ld_reduce / multimem.st: the NVSwitch sums the W gradient
+ * copies and replicates the new weights, halving the NVLink bytes of the peer-memory path.
+ * The callback is invoked collectively (every rank, same order, same sizes) from inside a store
+ * call; it fills *local, peers[0..world) (peers[rank] == *local) and *multicast (NULL if the
+ * fabric has no multicast) and returns 0, or non-zero to make the store fall back to its own
+ * allocations.  The memory must stay valid until b200kv_free.  No counterpart in the reference
+ * (its NCCL store lets NCCL own all exchange buffers, src/kvstore/kvstore_nccl.h:496-506). */
+typedef int (*b200kv_symm_alloc_fn)(void* ctx, size_t bytes, void** local, void** peers, void** multicast);
+int b200kv_set_symmetric_allocator(b200kv_handle h, b200kv_symm_alloc_fn fn, void* ctx);
+
 /* KVStoreLocal::LookupKeys (kvstore_local.h:449-457): string keys -> int keys.  create != 0
  * registers unknown names (init); otherwise an unknown name is an error. Mixing int and string
  * keys in one store is an error (kvstore_local.h:322-325). */

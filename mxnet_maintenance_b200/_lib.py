@@ -38,6 +38,7 @@ SIGNATURES = {
     "b200kv_free": [_VP],
     "b200kv_set_stream": [_VP, _VP],
     "b200kv_wait": [_VP],
+    "b200kv_set_symmetric_allocator": [_VP, _VP, _VP],
     "b200kv_comm_unique_id": [C.c_char_p],
     "b200kv_comm_init": [_VP, C.c_char_p],
     "b200kv_lookup_keys": [_VP, _I, C.POINTER(C.c_char_p), _I, _PI],

@@ -59,6 +59,12 @@ int b200kv_set_stream(b200kv_handle h, void* cuda_stream) {
   API_END();
 }
 
+int b200kv_set_symmetric_allocator(b200kv_handle h, b200kv_symm_alloc_fn fn, void* ctx) {
+  API_BEGIN();
+  S(h)->set_symmetric_allocator(fn, ctx);
+  API_END();
+}
+
 int b200kv_wait(b200kv_handle h) {
   API_BEGIN();
   S(h)->wait();

@@ -57,14 +57,22 @@ TensorView view_of(const DLManagedTensor* t, int device_id, const char* what);
 struct DevBuf {
   void* p = nullptr;
   size_t bytes = 0;
+  bool owned = true;   // false: memory provided by the host side (symmetric allocator), never freed here
   DevBuf() = default;
   DevBuf(const DevBuf&) = delete;
   DevBuf& operator=(const DevBuf&) = delete;
   ~DevBuf() { release(); }
   void release() {
-    if (p) cudaFree(p);
+    if (p && owned) cudaFree(p);
     p = nullptr;
     bytes = 0;
+    owned = true;
+  }
+  void adopt(void* ptr, size_t n) {
+    release();
+    p = ptr;
+    bytes = n;
+    owned = false;
   }
   // returns true when the buffer was (re)allocated; contents are NOT preserved
   bool reserve(size_t n) {

@@ -44,8 +44,12 @@ struct MtaArgs {
   // wait for every rank's signal
   const P2PFlags* sync;
   uint32_t epoch;
-  int sync_mode;
+  int sync_mode;   // kSync* bits
 };
+// sync_mode bits: the two barriers, and NVLS multicast addressing of the gradient / out sections
+// (multimem.ld_reduce / multimem.st; vector path only — multicast buffers are 16-byte aligned
+// bucket slots whose sizes the store pads to whole vectors)
+enum SyncBits { kSyncWaitReady = 1, kSyncSignalDone = 2, kSyncMcOut = 4, kSyncMcGrad = 8 };
 
 inline size_t mta_blob_words(int nt, int ngrad, int nout) {
   return static_cast<size_t>(nt) * static_cast<size_t>(ngrad + nout + 6);

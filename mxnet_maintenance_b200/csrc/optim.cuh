@@ -50,6 +50,47 @@ __device__ __forceinline__ float ld1(const __half* p) { return __half2float(*p);
 __device__ __forceinline__ void st1(float* p, float v) { *p = v; }
 __device__ __forceinline__ void st1(__half* p, float v) { *p = __float2half_rn(v); }
 
+// NVLS (NVLink SHARP): a load from a MULTICAST address returns the sum of that element over every
+// GPU bound to the multicast object, reduced inside the NVSwitch; a store to it lands on every GPU.
+// One such load replaces W-1 peer loads (the reduce-scatter half), one such store W-1 peer stores
+// (the all-gather half): NVLink bytes per GPU and direction drop from 2(W-1)/W*S to S.  The order
+// of the in-switch additions is not specified, so this path matches the reference within the fp32
+// tolerance rather than bit for bit.
+__device__ __forceinline__ void mc_ld4(const float* p, float (&v)[4]) {
+  asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0,%1,%2,%3}, [%4];"
+               : "=f"(v[0]), "=f"(v[1]), "=f"(v[2]), "=f"(v[3]) : "l"(p) : "memory");
+}
+__device__ __forceinline__ void mc_ld4(const __half* p, float (&v)[4]) {
+  uint32_t a, b;
+  asm volatile("multimem.ld_reduce.relaxed.sys.global.add.acc::f32.v2.f16x2 {%0,%1}, [%2];"
+               : "=r"(a), "=r"(b) : "l"(p) : "memory");
+  const float2 x = __half22float2(*reinterpret_cast<const __half2*>(&a));
+  const float2 y = __half22float2(*reinterpret_cast<const __half2*>(&b));
+  v[0] = x.x; v[1] = x.y; v[2] = y.x; v[3] = y.y;
+}
+__device__ __forceinline__ void mc_st4(float* p, const float (&v)[4]) {
+  asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(p), "f"(v[0]), "f"(v[1]),
+               "f"(v[2]), "f"(v[3]) : "memory");
+}
+__device__ __forceinline__ void mc_st4(__half* p, const float (&v)[4]) {
+  const __half2 a = __floats2half2_rn(v[0], v[1]);
+  const __half2 b = __floats2half2_rn(v[2], v[3]);
+  asm volatile("multimem.st.relaxed.sys.global.v2.f16x2 [%0], {%1,%2};" ::"l"(p),
+               "r"(*reinterpret_cast<const uint32_t*>(&a)), "r"(*reinterpret_cast<const uint32_t*>(&b)) : "memory");
+}
+__device__ __forceinline__ float mc_ld1(const float* p) {
+  float v;
+  asm volatile("multimem.ld_reduce.relaxed.sys.global.add.f32 %0, [%1];" : "=f"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void mc_st1(float* p, float v) {
+  asm volatile("multimem.st.relaxed.sys.global.f32 [%0], %1;" ::"l"(p), "f"(v) : "memory");
+}
+// There is no scalar f16 multimem form: the store rounds multicast chunks up to whole 4-element
+// vectors (inside the zero padding of a 64-element bucket slot), so fp16 never takes this path.
+__device__ __forceinline__ float mc_ld1(const __half*) { __trap(); return 0.f; }
+__device__ __forceinline__ void mc_st1(__half*, float) { __trap(); }
+
 // value of x after a round trip through the tensor's element type
 template <typename T> __device__ __forceinline__ float round_to(float x);
 template <> __device__ __forceinline__ float round_to<float>(float x) { return x; }
@@ -87,7 +128,8 @@ template <typename T, int NG>
 __device__ __forceinline__ void grad4(const MtaArgs& a, const T* const* gp, int t, int64_t e,
                                       float (&g)[4]) {
   if constexpr (NG == 1) {
-    ld4(gp[0] + e, g);
+    if (a.sync_mode & kSyncMcGrad) mc_ld4(gp[0] + e, g);
+    else ld4(gp[0] + e, g);
   } else if constexpr (NG == 0) {
     ld4(reinterpret_cast<const T*>(sec_grad(a, 0)[t]) + e, g);
     for (int i = 1; i < a.ngrad; i += 4) {
@@ -124,6 +166,7 @@ __device__ __forceinline__ void grad4(const MtaArgs& a, const T* const* gp, int 
 }
 template <typename T, int NG>
 __device__ __forceinline__ float grad1(const MtaArgs& a, int t, int64_t e) {
+  if (NG == 1 && (a.sync_mode & kSyncMcGrad)) return mc_ld1(reinterpret_cast<const T*>(sec_grad(a, 0)[t]) + e);
   float g = ld1(reinterpret_cast<const T*>(sec_grad(a, 0)[t]) + e);
   if (NG != 1) {
     for (int i = 1; i < a.ngrad; i += 4) {
@@ -530,8 +573,10 @@ mta_kernel(const MtaArgs a, const Op op, const float* __restrict__ gscale,
           if (F.write_s0) st4(s0p + e, s0[u]);
           if (F.write_s1) st4(s1p + e, s1[u]);
           if (F.write_w) st4(wp + e, w[u]);
-          if (F.write_out)
-            for (int k = 0; k < a.nout; ++k) st4(reinterpret_cast<T*>(sec_out(a, k)[t]) + e, w[u]);
+          if (F.write_out) {
+            if (a.sync_mode & kSyncMcOut) mc_st4(reinterpret_cast<T*>(sec_out(a, 0)[t]) + e, w[u]);
+            else for (int k = 0; k < a.nout; ++k) st4(reinterpret_cast<T*>(sec_out(a, k)[t]) + e, w[u]);
+          }
         }
       }
       }
@@ -551,8 +596,10 @@ mta_kernel(const MtaArgs a, const Op op, const float* __restrict__ gscale,
       if (F.write_s0) s0p[e] = s0;
       if (F.write_s1) s1p[e] = s1;
       if (F.write_w) st1(wp + e, w);
-      if (F.write_out)
-        for (int k = 0; k < a.nout; ++k) st1(reinterpret_cast<T*>(sec_out(a, k)[t]) + e, w);
+      if (F.write_out) {
+        if (a.sync_mode & kSyncMcOut) mc_st1(reinterpret_cast<T*>(sec_out(a, 0)[t]) + e, w);
+        else for (int k = 0; k < a.nout; ++k) st1(reinterpret_cast<T*>(sec_out(a, k)[t]) + e, w);
+      }
     }
 
     if (F.nred > 0) {

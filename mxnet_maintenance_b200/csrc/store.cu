@@ -62,7 +62,7 @@ Store::~Store() {
   cudaStreamSynchronize(stream_);
   for (auto& sp : segs_) {   // unmap the peers' buffers before our own are freed
     Segment::P2P& P = sp->p2p;
-    if (!P.ok) continue;
+    if (!P.ok || P.symmetric) continue;   // symmetric mappings belong to the host-side allocator
     for (int k = 0; k < world_; ++k) {
       if (k == rank_) continue;
       if (P.g[k]) cudaIpcCloseMemHandle(P.g[k]);
@@ -195,7 +195,15 @@ void Store::seal() {
     s->slice = s->total / world_;
     s->keys = ks;
     const size_t es = dtype_size(dt);
-    s->wbuf.reserve(static_cast<size_t>(s->total) * es);
+    {
+      void* peers[kMaxCopies] = {nullptr};
+      void* mc = nullptr;
+      if (alloc_exchange(s->wbuf, static_cast<size_t>(s->total) * es, peers, &mc)) {
+        s->p2p.symmetric = true;
+        for (int k = 0; k < world_; ++k) s->p2p.w[k] = peers[k];
+        s->p2p.mc_w = mc;
+      }
+    }
     CUDA_OK(cudaMemsetAsync(s->wbuf.p, 0, static_cast<size_t>(s->total) * es, stream_));
     for (int k : ks) {
       KeyInfo& ki = keys_[k];
@@ -309,6 +317,10 @@ DensePlan& Store::plan_for(int seg, const std::vector<int>& keys, int ngrad, int
     // shard range relative to the tensor's first element
     sb[t] = std::min(std::max(lo - ki.off, int64_t(0)), ki.size);
     se[t] = std::max(std::min(hi - ki.off, ki.size), sb[t]);
+    // whole 4-element vectors: a tensor's last vector may reach into the zero padding of its
+    // 64-element slot (multicast accesses have no scalar fp16 form; zeros stay zeros under every
+    // optimizer here)
+    if (se[t] == ki.size && se[t] > sb[t]) se[t] = (se[t] + 3) / 4 * 4;
     if (world_ > 1)
       for (int r = 0; r < world_; ++r) {
         const int64_t plo = std::max(ki.off, r * s.slice), phi = std::min(ki.off + ki.size, (r + 1) * s.slice);
@@ -370,8 +382,8 @@ void Store::update_chunks(DensePlan& p, const ChunkPlan& cp, const MtaCall& call
       float* sums = p.sums.as<float>();
       float* ratio = sums + 2 * static_cast<size_t>(c.nt);
       MtaCall c1 = c, c2 = c;
-      c1.sync_mode = c.sync_mode & 1;   // pass 1 is the first reader of the (peer) gradients
-      c2.sync_mode = c.sync_mode & 2;   // pass 2 is the last writer of the (peer) weights
+      c1.sync_mode = c.sync_mode & (kSyncWaitReady | kSyncMcGrad);   // pass 1: first reader of the gradients
+      c2.sync_mode = c.sync_mode & (kSyncSignalDone | kSyncMcOut);   // pass 2: last writer of the weights
       const bool keep_u = segs_[p.seg]->xbuf.p != nullptr;
       launches_ += launch_lamb1(c1, sc_, gscale, partials, keep_u);
       launches_ += launch_reduce_partials(partials, cp, 2, sums, stream_);
@@ -514,10 +526,7 @@ void Store::run_class(Mode mode, DensePlan& p, const std::vector<const Entry*>& 
   }
 
   // ---------------- world > 1: pack -> reduce-scatter -> sharded update -> all-gather -> unpack
-  if (s.gbuf.p == nullptr && push) {
-    s.gbuf.reserve(static_cast<size_t>(s.total) * es);
-    CUDA_OK(cudaMemsetAsync(s.gbuf.p, 0, static_cast<size_t>(s.total) * es, stream_));
-  }
+  if (s.gbuf.p == nullptr && push) alloc_gbuf(s);
   if (push && has_opt() && p.full_segment) {
     if (!s.p2p.tried) setup_p2p(s);
     if (s.p2p.ok) {
@@ -617,8 +626,65 @@ void Store::run_class(Mode mode, DensePlan& p, const std::vector<const Entry*>& 
 // ---- peer-memory path --------------------------------------------------------------------------------
 // Map every rank's gradient bucket, weight buffer and flag block into this process (CUDA IPC over
 // NVLink peer access).  All ranks must agree on the outcome, so the result is min-reduced.
+bool Store::alloc_exchange(DevBuf& buf, size_t bytes, void** peers, void** mc) {
+  if (symm_alloc_ != nullptr && world_ > 1 && world_ <= kMaxCopies) {
+    void* local = nullptr;
+    void* pp[kMaxCopies] = {nullptr};
+    void* m = nullptr;
+    if (symm_alloc_(symm_ctx_, bytes, &local, pp, &m) == 0 && local != nullptr) {
+      buf.adopt(local, bytes);
+      for (int k = 0; k < world_; ++k) peers[k] = pp[k];
+      *mc = m;
+      return true;
+    }
+  }
+  buf.reserve(bytes);
+  return false;
+}
+
+void Store::alloc_gbuf(Segment& s) {
+  const size_t bytes = static_cast<size_t>(s.total) * dtype_size(s.dtype);
+  void* peers[kMaxCopies] = {nullptr};
+  void* mc = nullptr;
+  if (alloc_exchange(s.gbuf, bytes, peers, &mc) && s.p2p.symmetric) {
+    for (int k = 0; k < world_; ++k) s.p2p.g[k] = peers[k];
+    s.p2p.mc_g = mc;
+  } else {
+    s.p2p.symmetric = false;   // mixed provenance: use the IPC path
+  }
+  CUDA_OK(cudaMemsetAsync(s.gbuf.p, 0, bytes, stream_));
+}
+
 void Store::setup_p2p(Segment& s) {
   s.p2p.tried = true;
+  if (s.p2p.symmetric) {
+    // symmetric memory is already mapped everywhere: only the flag block is missing
+    Segment::P2P& P = s.p2p;
+    void* peers[kMaxCopies] = {nullptr};
+    void* mc = nullptr;
+    if (alloc_exchange(P.local_flags, 2u << 20, peers, &mc)) {
+      CUDA_OK(cudaMemsetAsync(P.local_flags.p, 0, 256, stream_));
+      for (int k = 0; k < world_; ++k) P.flags[k] = static_cast<uint32_t*>(peers[k]);
+      // every rank's flags must be zero before anyone signals: a tiny all-reduce is the barrier
+      DevBuf tmp;
+      tmp.reserve(16);
+      CUDA_OK(cudaMemsetAsync(tmp.p, 0, 16, stream_));
+      NCCL_OK(NcclApi::get().AllReduce(tmp.p, tmp.p, 1, ncclFloat32, ncclSum,
+                                       reinterpret_cast<ncclComm_t>(comm_), stream_));
+      CUDA_OK(cudaStreamSynchronize(stream_));
+      P2PFlags h;
+      std::memset(&h, 0, sizeof(h));
+      for (int k = 0; k < world_; ++k) h.flags[k] = P.flags[k];
+      h.world = world_;
+      h.rank = rank_;
+      P.dev_sync.reserve(sizeof(P2PFlags));
+      CUDA_OK(cudaMemcpy(P.dev_sync.p, &h, sizeof(h), cudaMemcpyHostToDevice));
+      P.ok = true;
+      return;
+    }
+    P.symmetric = false;
+    P.local_flags.release();
+  }
   const char* env = getenv("B200KV_P2P");
   if (env && env[0] == '0') return;
   if (world_ > kMaxCopies) return;
@@ -627,7 +693,9 @@ void Store::setup_p2p(Segment& s) {
   ncclComm_t comm = reinterpret_cast<ncclComm_t>(comm_);
   struct Handles { cudaIpcMemHandle_t g, w, f, s; };
   const size_t seg_bytes = static_cast<size_t>(s.total) * dtype_size(s.dtype);
-  P.local_stage.reserve(std::max<size_t>(seg_bytes, 2u << 20));
+  const char* push_e = getenv("B200KV_PUSH");
+  const bool want_stage = push_e && push_e[0] == '1';   // only the push variant needs W x slice of staging
+  P.local_stage.reserve(want_stage ? std::max<size_t>(seg_bytes, 2u << 20) : (2u << 20));
   P.local_flags.reserve(2u << 20);   // its own 2 MiB allocation: IPC maps whole allocations
   CUDA_OK(cudaMemsetAsync(P.local_flags.p, 0, 256, stream_));
   Handles mine;
@@ -712,14 +780,23 @@ void Store::run_class_p2p(DensePlan& p, Segment& s, const std::vector<const Entr
   // bucket into their owners' staging areas (NVLink writes only), then the owner sums W local copies.
   // Measured equal at 8 GPUs for SGD (0.327 vs 0.325 ms) and slower for LAMB (extra local pass).
   const bool push_rs = push_env && !staged;
+  // NVLS: with symmetric buffers and a multicast mapping the NVSwitch does the summing and the
+  // replication (multimem.ld_reduce / multimem.st) — one switch-reduced load per element instead
+  // of W-1 peer loads, one multicast store instead of W-1 peer stores.  Opt-in with B200KV_NVLS=1.
+  static const bool nvls_env = [] { const char* e = getenv("B200KV_NVLS"); return e && e[0] == '1'; }();
+  // fp32 only: the switch's fp16 additions were measured to round differently from the reference's
+  // round-to-nearest-even half adds (1-ulp differences at two ranks), so fp16 buckets keep peer loads.
+  const bool nvls = nvls_env && P.symmetric && P.mc_g != nullptr && P.mc_w != nullptr && !staged && !push_rs &&
+                    s.dtype == kF32;
   // gradient copy k of the element at flat offset `off`, as seen by the shard owner
   auto grad_src = [&](int k, int64_t off) -> const char* {
     if (!push_rs) return static_cast<const char*>(P.g[k]) + off * es;
     if (k == rank_) return static_cast<const char*>(s.gbuf.p) + off * es;
     return static_cast<const char*>(P.local_stage.p) + (static_cast<int64_t>(k) * s.slice + off - rank_ * s.slice) * es;
   };
-  const int upd_ng = prereduce ? 1 : W, upd_no = mp ? W : W - 1;
-  const size_t w_pack = mta_blob_words(nt, ng, 0), w_pre = prereduce ? mta_blob_words(nt, W, 0) : 0,
+  const int pre_ng = nvls ? 1 : W;
+  const int upd_ng = (prereduce || nvls) ? 1 : W, upd_no = nvls ? 1 : (mp ? W : W - 1);
+  const size_t w_pack = mta_blob_words(nt, ng, 0), w_pre = prereduce ? mta_blob_words(nt, pre_ng, 0) : 0,
                w_upd = mta_blob_words(nt, upd_ng, upd_no), w_unpack = mta_blob_words(nt, 1, no);
   uint64_t* host = ring_.begin((w_pack + w_pre + w_upd + w_unpack) * 8);
   const size_t o_pack = 0, o_pre = w_pack, o_upd = o_pre + w_pre, o_unpack = o_upd + w_upd;
@@ -731,10 +808,11 @@ void Store::run_class_p2p(DensePlan& p, Segment& s, const std::vector<const Entr
     }
   }
   if (prereduce) {
-    Blob b(host + o_pre, nt, W, 0);
+    Blob b(host + o_pre, nt, pre_ng, 0);
     for (int t = 0; t < nt; ++t) {
       const int64_t off = keys_[p.keys[t]].off;
-      for (int k = 0; k < W; ++k) b.G(k, t, grad_src(k, off));
+      if (nvls) b.G(0, t, static_cast<const char*>(P.mc_g) + off * es);
+      else for (int k = 0; k < W; ++k) b.G(k, t, grad_src(k, off));
       b.S(kSecW, t, at(s.gbuf, off, es));
     }
   }
@@ -743,11 +821,16 @@ void Store::run_class_p2p(DensePlan& p, Segment& s, const std::vector<const Entr
     for (int t = 0; t < nt; ++t) {
       const KeyInfo& ki = keys_[p.keys[t]];
       if (prereduce) u.G(0, t, at(s.gbuf, ki.off, es));
+      else if (nvls) u.G(0, t, static_cast<const char*>(P.mc_g) + ki.off * es);
       else for (int k = 0; k < W; ++k) u.G(k, t, grad_src(k, ki.off));
-      int o = 0;
-      for (int k = 0; k < W; ++k) {
-        if (!mp && k == rank_) continue;   // fp32: the W section already is the local weight buffer
-        u.O(o++, t, static_cast<char*>(P.w[k]) + ki.off * es);
+      if (nvls) {
+        u.O(0, t, static_cast<char*>(P.mc_w) + ki.off * es);   // one multicast store reaches every rank
+      } else {
+        int o = 0;
+        for (int k = 0; k < W; ++k) {
+          if (!mp && k == rank_) continue;   // fp32: the W section already is the local weight buffer
+          u.O(o++, t, static_cast<char*>(P.w[k]) + ki.off * es);
+        }
       }
       u.S(kSecW, t, mp ? at(s.master, ki.off - s.state_begin, 4) : at(s.wbuf, ki.off, 4));
       if (s.has_s0) u.S(kSecS0, t, at(s.s0, ki.off - s.state_begin, 4));
@@ -800,15 +883,17 @@ void Store::run_class_p2p(DensePlan& p, Segment& s, const std::vector<const Entr
   if (!fold) launches_ += launch_p2p_barrier(f, 0, stream_);       // every rank's bucket is complete
   if (prereduce) {
     MtaCall r = base;
-    r.blob = dev + o_pre; r.ngrad = W; r.nout = 0; r.plan = &p.shard; r.staged = staged;
-    if (fold) { r.sync = dsync; r.epoch = f.epoch; r.sync_mode = 1; }
+    r.blob = dev + o_pre; r.ngrad = pre_ng; r.nout = 0; r.plan = &p.shard; r.staged = staged;
+    if (fold) { r.sync = dsync; r.epoch = f.epoch; r.sync_mode = kSyncWaitReady; }
+    if (nvls) r.sync_mode |= kSyncMcGrad;
     launches_ += launch_copy(r, true, false);
   }
   prof_end();
 
   MtaCall u = base;
   u.blob = dev + o_upd; u.ngrad = upd_ng; u.nout = upd_no; u.plan = &p.shard; u.staged = staged && !prereduce;
-  if (fold) { u.sync = dsync; u.epoch = f.epoch; u.sync_mode = (prereduce ? 0 : 1) | 2; }
+  if (fold) { u.sync = dsync; u.epoch = f.epoch; u.sync_mode = (prereduce ? 0 : kSyncWaitReady) | kSyncSignalDone; }
+  if (nvls) u.sync_mode |= kSyncMcOut | (prereduce ? 0 : kSyncMcGrad);
   prof_begin(0);
   const float* gscale = opt_.clip_global_norm >= 0.f ? global_norm_scale(p, p.shard, u) : nullptr;
   update_chunks(p, p.shard, u, gscale);
@@ -1002,10 +1087,7 @@ DLManagedTensor* Store::view(int key, int which) {
   KV_CHECK(which >= 0 && which <= 3, "view selector must be 0..3");
   const size_t es = dtype_size(s.dtype);
   const bool grad = which == 1 || which == 3;
-  if (grad && s.gbuf.p == nullptr) {
-    s.gbuf.reserve(static_cast<size_t>(s.total) * es);
-    CUDA_OK(cudaMemsetAsync(s.gbuf.p, 0, static_cast<size_t>(s.total) * es, stream_));
-  }
+  if (grad && s.gbuf.p == nullptr) alloc_gbuf(s);
   KV_CHECK(!(which == 0 || which == 2) || !s.w_stale,
            "weight views must be taken before the first multi-precision update");
   ViewBox* b = new ViewBox();

@@ -49,6 +49,9 @@ struct Segment {
     void* g[kMaxCopies] = {nullptr};
     void* w[kMaxCopies] = {nullptr};
     uint32_t* flags[kMaxCopies] = {nullptr};
+    void* mc_g = nullptr;                  // NVLS multicast addresses of the bucket / weight segment
+    void* mc_w = nullptr;
+    bool symmetric = false;                // buffers came from the host's symmetric allocator
     void* stage[kMaxCopies] = {nullptr};   // every rank's staging area ([world][slice], push reduce-scatter)
     DevBuf local_stage;
     DevBuf local_flags;
@@ -76,6 +79,7 @@ class Store {
   ~Store();
 
   void set_stream(cudaStream_t s) { stream_ = s; }
+  void set_symmetric_allocator(b200kv_symm_alloc_fn fn, void* ctx) { symm_alloc_ = fn; symm_ctx_ = ctx; }
   void wait();
   void comm_init(const char id[128]);
   void lookup_keys(int num, const char* const* names, bool create, int* out);
@@ -149,6 +153,10 @@ class Store {
   const float* global_norm_scale(DensePlan& p, const ChunkPlan& cp, const MtaCall& gcall);
   void set_hyper_rsp(int key, float lr, float wd, int step);
   void setup_p2p(Segment& s);
+  // allocate `bytes` for `buf`: through the symmetric allocator when one is set (filling peers / mc),
+  // else with cudaMalloc.  Returns true when the memory is symmetric.
+  bool alloc_exchange(DevBuf& buf, size_t bytes, void** peers, void** mc);
+  void alloc_gbuf(Segment& s);
   void run_class_p2p(DensePlan& p, Segment& s, const std::vector<const Entry*>& ents, bool pull,
                      bool g_alias, bool o_alias);
   bool has_opt() const { return opt_.kind != B200KV_OPT_NONE; }
@@ -170,6 +178,8 @@ class Store {
   DevBuf gnorm_;           // float[2]: scale, norm of the last clipped push
   bool gnorm_valid_ = false;
   int64_t launches_ = 0;
+  b200kv_symm_alloc_fn symm_alloc_ = nullptr;
+  void* symm_ctx_ = nullptr;
   std::unordered_map<int, std::unique_ptr<BoundCall>> bound_;
   int next_bound_ = 1;
   bool profiling_ = false;

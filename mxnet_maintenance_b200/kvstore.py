@@ -240,6 +240,44 @@ class B200(KVStoreBase):
         obj = [buf.raw]
         torch.distributed.broadcast_object_list(obj, src=0)
         check_call(self._lib.b200kv_comm_init(self._h, C.create_string_buffer(obj[0], 128)))
+        self._install_symmetric_allocator()
+
+    def _install_symmetric_allocator(self):
+        """Plumbing for the NVLS path: let the store take its exchange buffers from
+        torch.distributed._symmetric_memory, which maps the same allocation into every rank and binds
+        it to an NVSwitch multicast object.  The library only receives raw addresses (local, peers,
+        multicast); all arithmetic stays in its own kernels.  Skipped (the store then uses CUDA IPC
+        peer mappings) unless B200KV_NVLS=1 and the torch build has symmetric memory."""
+        if os.environ.get("B200KV_NVLS", "0") != "1":
+            return
+        try:
+            import torch.distributed._symmetric_memory as symm_mem
+            group = torch.distributed.group.WORLD
+            gname = group.group_name
+        except Exception:
+            return
+        dev = torch.device("cuda", self._device)
+        world, keep = self._world, []
+        CB = C.CFUNCTYPE(C.c_int, C.c_void_p, C.c_size_t, C.POINTER(C.c_void_p), C.POINTER(C.c_void_p),
+                         C.POINTER(C.c_void_p))
+
+        def alloc(_ctx, nbytes, local, peers, mc):
+            try:
+                t = symm_mem.empty(int(nbytes), dtype=torch.uint8, device=dev)
+                hdl = symm_mem.rendezvous(t, gname)
+                ptrs = list(hdl.buffer_ptrs)
+                if len(ptrs) != world or ptrs[hdl.rank] != t.data_ptr():
+                    return 1
+                keep.append((t, hdl))
+                local[0] = t.data_ptr()
+                for k in range(world):
+                    peers[k] = ptrs[k]
+                mc[0] = hdl.multicast_ptr if getattr(hdl, "multicast_ptr", 0) else None
+                return 0
+            except Exception:
+                return 1
+        self._symm_cb, self._symm_keep = CB(alloc), keep
+        check_call(self._lib.b200kv_set_symmetric_allocator(self._h, C.cast(self._symm_cb, C.c_void_p), None))
 
     def _keys(self, keys, use_str, create=False):
         """int keys for the C ABI; string keys are mapped by the store (LookupKeys)."""

@@ -546,18 +546,26 @@ def run_b200(args):
         # (NCCL path, or LAMB whose peer traffic is split over a reduce pass and the last update
         # pass) the link bytes are spread over the step, so the step time is the denominator
         p2p_on = os.environ.get("B200KV_P2P", "1") != "0" and kind != "lamb"
+        nv_env = os.environ.get("B200KV_NVLS")
+        nvls_on = (os.environ.get("B200KV_P2P", "1") != "0" and dt == "f32" and
+                   (nv_env == "1" or (nv_env is None and world >= 4 and kind != "lamb")))
         roof = {"bound": "nvlink", "achieved": ach_kernel if p2p_on else ach_step, "peak": 770.0, "unit": "GB/s",
                 "frac": (ach_kernel if p2p_on else ach_step) / 770.0, "traffic": None,
                 "kernel": ("mta_kernel over peer memory: fused reduce-scatter + %s update + all-gather" % kind)
                           if p2p_on else "ncclReduceScatter + sharded update + ncclAllGather",
+                "exchange": "nvls multicast (multimem.ld_reduce / multimem.st)" if nvls_on else
+                            ("peer memory loads/stores" if os.environ.get("B200KV_P2P", "1") != "0" else "nccl"),
+                "nvls_actual_link_bytes_per_direction": sbytes * (1.0 + 1.0 / world) if nvls_on else None,
                 "link_bytes_per_direction_per_step": link_bytes, "kernel_ms_per_step": k_ms,
                 "step_achieved_GBps": ach_step, "step_frac_of_measured_peak": ach_step / 770.0,
                 "step_frac_of_nominal_900": ach_step / 900.0,
                 "step_lower_bound_ms_nominal": (link_bytes / 900e9 + t_upd) * 1e3,
                 "phase_ms_per_step": {k: v[0] / max(v[1], 1) for k, v in phases.items()},
                 "peak_source": "measured peer copy 770 GB/s per direction (B200_PROFILING.md); nominal 900",
-                "note": "achieved = bytes crossing NVLink per direction / fused-kernel time (CUDA events "
-                        "recorded by the library around the kernel on rank 0)"}
+                "note": "achieved = algorithmic collective bytes per direction (SURVEY 8d: reduce-scatter + "
+                        "all-gather, 2*S*(N-1)/N) / fused-kernel time (CUDA events recorded by the library "
+                        "around the kernel on rank 0); with NVLS the switch sums and replicates, so fewer "
+                        "bytes actually cross the links and the fraction can approach or exceed 1"}
 
     line = {
         "metric": "grad-sync+update steps/s", "value": sps, "unit": "steps/s", "n_gpus": world,

@@ -247,8 +247,10 @@ class B200(KVStoreBase):
         torch.distributed._symmetric_memory, which maps the same allocation into every rank and binds
         it to an NVSwitch multicast object.  The library only receives raw addresses (local, peers,
         multicast); all arithmetic stays in its own kernels.  Skipped (the store then uses CUDA IPC
-        peer mappings) unless B200KV_NVLS=1 and the torch build has symmetric memory."""
-        if os.environ.get("B200KV_NVLS", "0") != "1":
+        peer mappings) when B200KV_NVLS=0, below 4 ranks (unless B200KV_NVLS=1) or when the torch
+        build has no symmetric memory."""
+        env = os.environ.get("B200KV_NVLS")
+        if env == "0" or (env != "1" and self._world < 4):
             return
         try:
             import torch.distributed._symmetric_memory as symm_mem

@@ -147,3 +147,65 @@ def test_known_answer_row_sparse(oracle):
     ri, rv = oracle.sparse_retain(idx, val, oracle.unique([19, 0, 0, 5, 19]))
     assert ri.tolist() == [0, 5, 19]
     assert (rv == full[[0, 5, 19]]).all()
+
+
+def test_bound_step_refresh_equals_resolve_step():
+    """BoundStep._refresh (the vectorised per-step scalar path of bind_pushpull) must ship exactly the
+    floats that the reference-order resolve_step produces — checked on the CPU with a fake library
+    that records the b200kv_set_hyper arguments."""
+    import ctypes as C
+    from mxnet_maintenance_b200.kvstore import BoundStep
+
+    class Sched:
+        base_lr = 0.02
+
+        def __call__(self, n):
+            return self.base_lr * (0.9 ** n)
+
+    class FakeLib:
+        def __init__(self):
+            self.calls = []
+
+        def b200kv_set_hyper(self, h, n, keys, lrs, wds, steps):
+            f = C.cast(lrs, C.POINTER(C.c_float))
+            g = C.cast(wds, C.POINTER(C.c_float))
+            self.calls.append(([f[i] for i in range(n)], [g[i] for i in range(n)], [steps[i] for i in range(n)]))
+            return 0
+
+        def b200kv_run_bound(self, h, bid):
+            return 0
+
+    class FakeKV:
+        def __init__(self, optimizer):
+            self._lib, self._h = FakeLib(), None
+            self._updater = opt.Updater(optimizer)
+
+        def _keys(self, keys, use_str, create=False):
+            return (C.c_int * len(keys))(*keys)
+
+        def _send_optimizer(self):
+            pass
+
+    keys = list(range(7))
+    for kind in ("sgd", "adam", "lamb"):
+        def make():
+            O = {"sgd": opt.SGD, "adam": opt.Adam, "lamb": opt.LAMB}[kind]
+            return O(learning_rate=0.02, lr_scheduler=Sched(), wd=1e-3,
+                     param_dict={k: _P(1.0 + 0.25 * (k % 3), 0.5 * (k % 2)) for k in keys})
+        o_ref, o_fast = make(), make()
+        kv = FakeKV(o_fast)
+        opt.resolve_step(o_fast, keys)            # what bind_pushpull does for the first replay
+        step = BoundStep(kv, 1, keys, None)
+        expect = [opt.resolve_step(o_ref, keys)]
+        step()                                    # first replay: scalars already resolved by bind
+        for it in range(3):
+            if it == 1:
+                o_ref.param_dict[2].lr_mult = 3.0
+                o_fast.param_dict[2].lr_mult = 3.0
+            lrs, wds, steps = opt.resolve_step(o_ref, keys)
+            step()
+            got = kv._lib.calls[-1]
+            f32 = lambda xs: [C.c_float(x).value for x in xs]
+            assert got[0] == f32(lrs) and got[1] == f32(wds) and got[2] == steps, (kind, it)
+        assert o_fast.num_update == o_ref.num_update == 4
+        assert o_fast._index_update_count == o_ref._index_update_count

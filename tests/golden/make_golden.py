@@ -96,6 +96,26 @@ def cases(o):
     out["rsp_w2"], out["rsp_mom2"] = W.copy(), mom.copy()
     ri, rv = o.sparse_retain(idx, gr, [0, 1, 4, 40, 41, 63])
     out["retain_idx"], out["retain_val"] = ri, rv
+    # _multi_adamw_update (fp32), 3 steps incl. one skipped (non-finite loss scale)
+    w = arrs()
+    mean = [np.zeros(s, np.float32) for s in sizes]
+    var = [np.zeros(s, np.float32) for s in sizes]
+    out["adamw_w0"] = np.concatenate(w)
+    for step, rs in enumerate([0.5, float("inf"), 0.25]):
+        g = arrs(1e-2)
+        out["adamw_g%d" % step] = np.concatenate(g)
+        o.multi_adamw(w, g, mean, var, None, lrs, wds, [1.0, 0.5, 2.0, 1.0, 1.0, 0.1], rescale=rs, clip=0.004)
+    out["adamw_w3"], out["adamw_var3"] = np.concatenate(w), np.concatenate(var)
+    # multi_lars
+    l_in = [rng.uniform(0.01, 0.2, 40).astype(np.float32), (rng.uniform(0, 5, 40) * (rng.random(40) > 0.2)).astype(np.float32),
+            (rng.uniform(0, 1e-2, 40) * (rng.random(40) > 0.2)).astype(np.float32), rng.uniform(0, 1e-3, 40).astype(np.float32)]
+    out["lars_in"] = np.stack(l_in)
+    out["lars_out"] = o.multi_lars(l_in[0], l_in[1], l_in[2], l_in[3], 0.001, 1e-8, 0.5)
+    # lazy row-sparse AdaGrad
+    Wa, ha = out["rsp_w0"].copy(), np.zeros_like(out["rsp_w0"])
+    o.adagrad_rsp(Wa, ha, idx, gr, 0.1, 1e-7, 0.5)
+    o.adagrad_rsp(Wa, ha, idx, gr, 0.1, 1e-7, 0.5, 0.003)
+    out["adagrad_rsp_w2"], out["adagrad_rsp_h2"] = Wa, ha
     out["sizes"] = np.asarray(sizes, np.int64)
     return out
 

@@ -167,3 +167,39 @@ def test_cuda_clip_global_norm(oracle, max_norm):
     if max_norm > 1:
         for d, a in zip(dev, arrs):
             assert d.cpu().numpy().tobytes() == a.tobytes()       # scale == 1: untouched bits
+
+
+ETAS = [1.0, 0.5, 2.0, 1.0, 1.0, 0.1]
+
+
+def test_oracle_adamw_lars_adagrad(oracle):
+    w = split(G["adamw_w0"])
+    mean = [np.zeros(s, np.float32) for s in SIZES]
+    var = [np.zeros(s, np.float32) for s in SIZES]
+    for step, rs in enumerate([0.5, float("inf"), 0.25]):
+        oracle.multi_adamw(w, split(G["adamw_g%d" % step]), mean, var, None, LRS, WDS, ETAS, rescale=rs, clip=0.004)
+    assert np.concatenate(w).tobytes() == G["adamw_w3"].tobytes()
+    assert np.concatenate(var).tobytes() == G["adamw_var3"].tobytes()
+    li = G["lars_in"]
+    assert oracle.multi_lars(li[0], li[1], li[2], li[3], 0.001, 1e-8, 0.5).tobytes() == G["lars_out"].tobytes()
+    W, h = G["rsp_w0"].copy(), np.zeros_like(G["rsp_w0"])
+    oracle.adagrad_rsp(W, h, G["rsp_idx"], G["rsp_g"], 0.1, 1e-7, 0.5)
+    oracle.adagrad_rsp(W, h, G["rsp_idx"], G["rsp_g"], 0.1, 1e-7, 0.5, 0.003)
+    assert W.tobytes() == G["adagrad_rsp_w2"].tobytes() and h.tobytes() == G["adagrad_rsp_h2"].tobytes()
+
+
+@pytest.mark.gpu
+def test_cuda_adamw_lars_golden():
+    import torch
+    from mxnet_maintenance_b200 import ops
+    w = _cuda(split(G["adamw_w0"]))
+    mean = _cuda([np.zeros(s, np.float32) for s in SIZES])
+    var = _cuda([np.zeros(s, np.float32) for s in SIZES])
+    for step, rs in enumerate([0.5, float("inf"), 0.25]):
+        ops.multi_adamw_update(w, _cuda(split(G["adamw_g%d" % step])), mean, var,
+                               torch.tensor([rs], device="cuda"), LRS, WDS, ETAS, clip_gradient=0.004)
+    assert _flat(w).tobytes() == G["adamw_w3"].tobytes()
+    assert _flat(var).tobytes() == G["adamw_var3"].tobytes()
+    li = [torch.from_numpy(np.ascontiguousarray(x)).cuda() for x in G["lars_in"]]
+    got = ops.multi_lars(li[0], li[1], li[2], li[3], 0.001, 1e-8, 0.5).cpu().numpy()
+    assert got.tobytes() == G["lars_out"].tobytes()

@@ -279,6 +279,7 @@ struct OpWorkspace {
   ChunkPlan plan;
   std::vector<int64_t> sizes;
   DevBuf partials, sums;
+  DevBuf xbuf;   // fp32 scratch for LAMB's update direction (one slot per tensor, 64-element aligned)
   std::mutex mu;
 };
 
@@ -324,7 +325,7 @@ struct Table {
 MtaCall make_call(OpWorkspace& w, int num, int dtype, void* const* weights, const void* const* grads,
                   float* const* s0, float* const* s1, float* const* w32, const float* lrs,
                   const float* wds, const float* aux0, const float* aux1, cudaStream_t stream,
-                  int device) {
+                  int device, const int64_t* x_offsets = nullptr) {
   KV_CHECK(dtype == kF32 || dtype == kF16, "dtype must be 0 (float32) or 2 (float16 + fp32 master)");
   const bool mp = dtype == kF16;
   KV_CHECK(!mp || w32 != nullptr, "float16 weights need weights32 master copies");
@@ -338,6 +339,7 @@ MtaCall make_call(OpWorkspace& w, int num, int dtype, void* const* weights, cons
     else t.Sx(kSecW, i, weights[i]);
     if (s0) t.Sx(kSecS0, i, s0[i]);
     if (s1) t.Sx(kSecS1, i, s1[i]);
+    if (x_offsets) t.Sx(kSecX, i, w.xbuf.as<float>() + x_offsets[i]);
     t.F2(kSecLrWd, i, lrs ? lrs[i] : 0.f, wds ? wds[i] : 0.f);
     t.F2(kSecAux, i, aux0 ? aux0[i] : 0.f, aux1 ? aux1[i] : 0.f);
   }
@@ -412,18 +414,26 @@ int b200kv_multi_lamb_update(int num, int dtype, void* const* weights, const voi
     c1[i] = 1.0f - powf(beta1, tf);
     c2[i] = 1.0f - powf(beta2, tf);
   }
+  // pass 1 leaves the update direction u in a scratch slot per tensor; pass 2 streams w, u -> w
+  std::vector<int64_t> xoff(num);
+  int64_t xtotal = 0;
+  for (int i = 0; i < num; ++i) {
+    xoff[i] = xtotal;
+    xtotal += (sizes[i] + 63) / 64 * 64;
+  }
+  w.xbuf.reserve(sizeof(float) * static_cast<size_t>(std::max<int64_t>(xtotal, 64)));
   MtaCall c = make_call(w, num, dtype, weights, grads, means, vars, weights32, lrs, wds, c1.data(),
-                        c2.data(), st, dev);
+                        c2.data(), st, dev, xoff.data());
   OptScalars s;
   s.beta1 = beta1; s.beta2 = beta2; s.eps = epsilon; s.rescale = rescale_grad; s.clip = clip_gradient;
   s.lower = lower_bound; s.upper = upper_bound; s.bias_correction = bias_correction;
   float* partials = w.partials.as<float>();
   float* sums = w.sums.as<float>();
   float* ratio = sums + 2 * static_cast<size_t>(num);
-  launch_lamb1(c, s, nullptr, partials);
+  launch_lamb1(c, s, nullptr, partials, true);
   launch_reduce_partials(partials, w.plan, 2, sums, st);
   launch_lamb_ratio(sums, num, lower_bound, upper_bound, ratio, st);
-  launch_lamb2(c, s, ratio);
+  launch_lamb2u(c, ratio);
   w.ring.end(st);
   API_END();
 }

@@ -64,11 +64,11 @@ int b200kv_version(int* out);
  * Reference block: include/mxnet/c_api.h:2720-3140, impl src/c_api/c_api.cc:2534-2975,
  * semantics src/kvstore/kvstore_local.h:226-343. */
 
-/* MXKVStoreCreate (c_api.h:2727) + KVStore::Create (src/kvstore/kvstore.cc:41-82).
+/* MXKVStoreCreate (c_api.h:2720) + KVStore::Create (src/kvstore/kvstore.cc:41-82).
  * device_id: CUDA ordinal this store drives.  rank/world_size: position among the cooperating
  * processes (MXKVStoreGetRank / MXKVStoreGetGroupSize). */
 int b200kv_create(int device_id, int rank, int world_size, b200kv_handle* out);
-/* MXKVStoreFree (c_api.h:2741) */
+/* MXKVStoreFree (c_api.h:2740) */
 int b200kv_free(b200kv_handle h);
 /* stream all subsequent work is enqueued on (a cudaStream_t passed as an integer/pointer) */
 int b200kv_set_stream(b200kv_handle h, void* cuda_stream);
@@ -100,19 +100,19 @@ int b200kv_set_symmetric_allocator(b200kv_handle h, b200kv_symm_alloc_fn fn, voi
 int b200kv_lookup_keys(b200kv_handle h, int num, const char* const* str_keys, int create,
                        int* out_keys);
 
-/* MXKVStoreInit (c_api.h:2752): copies each value into the store; duplicate key -> error
+/* MXKVStoreInit (c_api.h:2749): copies each value into the store; duplicate key -> error
  * (kvstore_local.h:229-232).  With several processes the value of rank 0 is broadcast. */
 int b200kv_init(b200kv_handle h, int num, const int* keys, DLManagedTensor* const* vals);
-/* MXKVStorePush (c_api.h:2790): entries with equal keys are device copies of one key
+/* MXKVStorePush (c_api.h:2776): entries with equal keys are device copies of one key
  * (GroupKVPairs, kvstore_local.h:417-447).  Reduce, then run the optimizer on the stored value,
  * or assign the merged value when none is set (kvstore_local.h:239-276). */
 int b200kv_push(b200kv_handle h, int num, const int* keys, DLManagedTensor* const* vals,
                 int priority);
-/* MXKVStorePullWithSparse (c_api.h:2830): copy the stored value into every out
+/* MXKVStorePullWithSparse (c_api.h:2805): copy the stored value into every out
  * (kvstore_local.h:278-292). */
 int b200kv_pull(b200kv_handle h, int num, const int* keys, DLManagedTensor* const* outs,
                 int priority);
-/* MXKVStorePushPull (c_api.h:2920): push then pull, fused into one pass
+/* MXKVStorePushPull (c_api.h:2947): push then pull, fused into one pass
  * (kvstore_local.h:336-343). */
 int b200kv_pushpull(b200kv_handle h, int vnum, const int* vkeys, DLManagedTensor* const* vals,
                     int onum, const int* okeys, DLManagedTensor* const* outs, int priority);
@@ -126,12 +126,12 @@ int b200kv_bind_pushpull(b200kv_handle h, int vnum, const int* vkeys, DLManagedT
 int b200kv_run_bound(b200kv_handle h, int id);
 int b200kv_unbind(b200kv_handle h, int id);
 
-/* MXKVStoreBroadcast (c_api.h:2880): init + pull (kvstore_local.h:327-334). */
+/* MXKVStoreBroadcast (c_api.h:2905): init + pull (kvstore_local.h:327-334). */
 int b200kv_broadcast(b200kv_handle h, int vnum, const int* vkeys, DLManagedTensor* const* vals,
                      int onum, const int* okeys, DLManagedTensor* const* outs, int priority);
 
 /* ---- optimizer on the store: replaces MXKVStoreSetUpdaterEx + the Python updater callback ----
- * (c_api.h:2985-3020; kvstore_local.h:259-267; python/mxnet/optimizer/optimizer.py:2070-2127).
+ * (c_api.h:2985-3027; kvstore_local.h:259-267; python/mxnet/optimizer/optimizer.py:2070-2127).
  * The host side keeps the Optimizer's scheduler / multiplier logic and ships resolved scalars,
  * exactly the attributes that reach multi_sgd_mom_update / adam_update / multi_lamb_update. */
 enum { B200KV_OPT_NONE = 0, B200KV_OPT_SGD = 1, B200KV_OPT_ADAM = 2, B200KV_OPT_LAMB = 3,
@@ -187,7 +187,7 @@ int b200kv_push_rsp(b200kv_handle h, int key, int ncopies, DLManagedTensor* cons
 int b200kv_rsp_merged_size(b200kv_handle h, int key, int64_t* nnr);
 int b200kv_rsp_merged_copy(b200kv_handle h, int key, DLManagedTensor* out_indices,
                            DLManagedTensor* out_values);
-/* MXKVStorePullRowSparse (c_api.h:2960; kvstore_local.h:294-314,468-512; kvstore_utils.cu:44-110;
+/* MXKVStorePullRowSparse (c_api.h:2868; kvstore_local.h:294-314,468-512; kvstore_utils.cu:44-110;
  * sparse_retain-inl.h:262-323): row_ids may be any shape / int or float dtype, unsorted, with
  * duplicates.  out_indices (int64) and out_values must hold at least numel(row_ids) rows;
  * *out_nnr receives the number of unique ids; rows absent from the store come back as zeros. */
@@ -195,7 +195,7 @@ int b200kv_row_sparse_pull(b200kv_handle h, int key, DLManagedTensor* row_ids,
                            DLManagedTensor* out_indices, DLManagedTensor* out_values,
                            int64_t* out_nnr, int priority);
 
-/* MXKVStoreGetType / GetRank / GetGroupSize / Barrier (c_api.h:3040-3100) */
+/* MXKVStoreGetType / GetRank / GetGroupSize / Barrier (c_api.h:3029-3086) */
 int b200kv_get_type(b200kv_handle h, const char** out);
 int b200kv_get_rank(b200kv_handle h, int* out);
 int b200kv_get_group_size(b200kv_handle h, int* out);
@@ -218,7 +218,10 @@ int b200kv_launch_count(b200kv_handle h, int64_t* out);
  * update_on_kvstore=False (python/mxnet/optimizer/optimizer.py:602-669,1316-1361).  Arrays are raw
  * device pointers; every pointer array has `num` entries; all updates are in place.
  * dtype: 0 = float32 everywhere; 2 = float16 weights/grads with float32 states and `weights32`
- * master copies (the multi_mp_* variants).  stream: cudaStream_t. */
+ * master copies (the multi_mp_* variants).  stream: cudaStream_t.
+ * Scratch (tensor tables, chunk lists, reduction partials) is kept per (current device, stream):
+ * calls on one stream reuse it in stream order, calls on different streams never share it, so the
+ * entry points may be used concurrently from several streams / threads. */
 
 /* multi_sgd_update / multi_sgd_mom_update / multi_mp_sgd_update / multi_mp_sgd_mom_update
  * (src/operator/optimizer_op-inl.h:207-380; registration optimizer_op.cc:322-506).
@@ -294,8 +297,10 @@ int b200kv_clip_global_norm(int num, int dtype, void* const* arrays, const int64
  * image — every GPU that loads libb200kv.so holds those 343,296 bytes until the process exits.
  * Limits (a clear error is returned beyond them): at most B200KV_STATIC_MAX_ARRAYS arrays and
  * B200KV_STATIC_MAX_CHUNKS chunks of 4096 elements (sum over arrays of ceil(size/4096)) per call.
- * The first call on each device looks up where that GPU placed the array; make that first call
- * before starting any stream capture.  All calls share the one array and it keeps whatever the
+ * The first call on each device looks up where that GPU placed the array (a one-time runtime query);
+ * make that first call before starting any stream capture.  That is all this sentence says: every
+ * call also copies its tables from host memory, and no statement is made about capturing calls in
+ * a CUDA graph.  All calls share the one array and it keeps whatever the
  * previous call wrote (nothing in it needs clearing between calls); two calls whose GPU work
  * overlaps — different streams, or different threads — would overwrite each other's tables, so
  * order them on one stream or with events.  `arrays`/`sizes` are host arrays; `out` is a device

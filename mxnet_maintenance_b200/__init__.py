@@ -6,7 +6,7 @@ library has not been built — there is no CPU fallback.
 """
 from . import _lib
 from ._lib import B200KVError
-from .base import KVStoreBase, create, HAVE_MXNET
+from ._mx_shim import KVStoreBase, create, HAVE_MXNET
 from .kvstore import B200, RowSparse
 from . import optimizer, ops, shapes
 

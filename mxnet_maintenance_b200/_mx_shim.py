@@ -1,4 +1,4 @@
-"""The plugin interface the store registers with.
+"""The plugin interface the store registers with (MXNet-absent stand-in: see below).
 
 Inside a real MXNet process this is ``mxnet.kvstore.KVStoreBase`` itself, so that
 ``mx.kv.create('b200')`` and ``gluon.Trainer(kvstore=...)`` find the class.  MXNet cannot be

@@ -2,7 +2,10 @@
 // b200kv_last_error(), like MXNet's API_BEGIN/API_END (include/mxnet/c_api_error.h:36-55).
 #include <cmath>
 #include <cstring>
+#include <map>
+#include <memory>
 #include <mutex>
+#include <vector>
 
 #include "nccl_dl.h"
 #include "store.h"
@@ -272,24 +275,28 @@ int b200kv_launch_count(b200kv_handle h, int64_t* out) {
 // =================================================================================================
 namespace {
 
-// Per-device workspace for the operator calls: the tensor table ring, a cached chunk plan (rebuilt
-// only when the size list changes) and the small reduction scratch.
+// Workspace of the operator calls, one per (device, stream): the tensor table ring, chunk plans cached
+// by size list, and the small reduction scratch.  Everything a launch reads is either immutable once
+// built (a cached plan), event-guarded (the table ring) or only rewritten by later work on the SAME
+// stream (partials, sums, LAMB's scratch), so calls on different streams never share mutable state
+// and a call with a new size list never rewrites a chunk list an earlier launch may still be reading.
 struct OpWorkspace {
   TableRing ring;
-  ChunkPlan plan;
-  std::vector<int64_t> sizes;
+  std::map<std::vector<int64_t>, std::unique_ptr<ChunkPlan>> plans;
+  ChunkPlan* plan = nullptr;   // the plan of the current call
   DevBuf partials, sums;
   DevBuf xbuf;   // fp32 scratch for LAMB's update direction (one slot per tensor, 64-element aligned)
   std::mutex mu;
 };
 
-OpWorkspace& workspace(int device) {
+OpWorkspace& workspace(int device, void* stream) {
   static std::mutex mu;
-  static OpWorkspace* ws[64] = {nullptr};
+  static std::map<std::pair<int, void*>, std::unique_ptr<OpWorkspace>> ws;
   std::lock_guard<std::mutex> lk(mu);
   KV_CHECK(device >= 0 && device < 64, "device ordinal out of range");
-  if (!ws[device]) ws[device] = new OpWorkspace();
-  return *ws[device];
+  auto& slot = ws[std::make_pair(device, stream)];
+  if (!slot) slot.reset(new OpWorkspace());
+  return *slot;
 }
 
 int current_device() {
@@ -298,15 +305,23 @@ int current_device() {
   return d;
 }
 
-void prepare_plan(OpWorkspace& w, int num, const int64_t* sizes) {
+void prepare_plan(OpWorkspace& w, int num, const int64_t* sizes, cudaStream_t stream) {
   std::vector<int64_t> sz(sizes, sizes + num);
-  if (sz != w.sizes || w.plan.nt != num) {
+  auto it = w.plans.find(sz);
+  if (it == w.plans.end()) {
+    if (w.plans.size() >= 64) {   // bound the cache; nothing may still read the plans being dropped
+      CUDA_OK(cudaStreamSynchronize(stream));
+      w.plans.clear();
+    }
+    std::unique_ptr<ChunkPlan> p(new ChunkPlan());
     std::vector<int64_t> b(num, 0);
-    w.plan.build(b, sz);
-    w.sizes = sz;
-    w.partials.reserve(sizeof(float) * 2 * static_cast<size_t>(std::max(w.plan.nchunks, 1)));
-    w.sums.reserve(sizeof(float) * (3 * static_cast<size_t>(num) + 4));
+    p->build(b, sz);
+    it = w.plans.emplace(std::move(sz), std::move(p)).first;
   }
+  w.plan = it->second.get();
+  // grow-only; DevBuf::reserve releases with cudaFree, which waits for the device to drain first
+  w.partials.reserve(sizeof(float) * 2 * static_cast<size_t>(std::max(w.plan->nchunks, 1)));
+  w.sums.reserve(sizeof(float) * (3 * static_cast<size_t>(num) + 4));
 }
 
 struct Table {
@@ -345,7 +360,7 @@ MtaCall make_call(OpWorkspace& w, int num, int dtype, void* const* weights, cons
   }
   MtaCall c;
   c.blob = w.ring.commit(stream);
-  c.plan = &w.plan;
+  c.plan = w.plan;
   c.nt = num; c.ngrad = ngl; c.nout = no; c.dtype = dtype; c.stream = stream; c.device = device;
   return c;
 }
@@ -361,10 +376,10 @@ int b200kv_multi_sgd_update(int num, int dtype, void* const* weights, const void
   API_BEGIN();
   if (num <= 0) return 0;
   const int dev = current_device();
-  OpWorkspace& w = workspace(dev);
-  std::lock_guard<std::mutex> lk(w.mu);
-  prepare_plan(w, num, sizes);
   cudaStream_t st = static_cast<cudaStream_t>(stream);
+  OpWorkspace& w = workspace(dev, stream);
+  std::lock_guard<std::mutex> lk(w.mu);
+  prepare_plan(w, num, sizes, st);
   MtaCall c = make_call(w, num, dtype, weights, grads, moms, nullptr, weights32, lrs, wds, nullptr,
                         nullptr, st, dev);
   OptScalars s;
@@ -382,10 +397,10 @@ int b200kv_multi_adam_update(int num, int dtype, void* const* weights, const voi
   API_BEGIN();
   if (num <= 0) return 0;
   const int dev = current_device();
-  OpWorkspace& w = workspace(dev);
-  std::lock_guard<std::mutex> lk(w.mu);
-  prepare_plan(w, num, sizes);
   cudaStream_t st = static_cast<cudaStream_t>(stream);
+  OpWorkspace& w = workspace(dev, stream);
+  std::lock_guard<std::mutex> lk(w.mu);
+  prepare_plan(w, num, sizes, st);
   MtaCall c = make_call(w, num, dtype, weights, grads, means, vars, weights32, lrs, wds, nullptr,
                         nullptr, st, dev);
   OptScalars s;
@@ -404,10 +419,10 @@ int b200kv_multi_lamb_update(int num, int dtype, void* const* weights, const voi
   API_BEGIN();
   if (num <= 0) return 0;
   const int dev = current_device();
-  OpWorkspace& w = workspace(dev);
-  std::lock_guard<std::mutex> lk(w.mu);
-  prepare_plan(w, num, sizes);
   cudaStream_t st = static_cast<cudaStream_t>(stream);
+  OpWorkspace& w = workspace(dev, stream);
+  std::lock_guard<std::mutex> lk(w.mu);
+  prepare_plan(w, num, sizes, st);
   std::vector<float> c1(num), c2(num);
   for (int i = 0; i < num; ++i) {
     const float tf = static_cast<float>(step_counts[i]);
@@ -431,7 +446,7 @@ int b200kv_multi_lamb_update(int num, int dtype, void* const* weights, const voi
   float* sums = w.sums.as<float>();
   float* ratio = sums + 2 * static_cast<size_t>(num);
   launch_lamb1(c, s, nullptr, partials, true);
-  launch_reduce_partials(partials, w.plan, 2, sums, st);
+  launch_reduce_partials(partials, *w.plan, 2, sums, st);
   launch_lamb_ratio(sums, num, lower_bound, upper_bound, ratio, st);
   launch_lamb2u(c, ratio);
   w.ring.end(st);
@@ -455,10 +470,10 @@ int b200kv_preloaded_multi_sgd_update(int num, int dtype, void* const* weights, 
   if (num <= 0) return 0;
   KV_CHECK(lrs_dev != nullptr && wds_dev != nullptr, "lrs / wds must be device arrays of `num` floats");
   const int dev = current_device();
-  OpWorkspace& w = workspace(dev);
-  std::lock_guard<std::mutex> lk(w.mu);
-  prepare_plan(w, num, sizes);
   cudaStream_t st = static_cast<cudaStream_t>(stream);
+  OpWorkspace& w = workspace(dev, stream);
+  std::lock_guard<std::mutex> lk(w.mu);
+  prepare_plan(w, num, sizes, st);
   MtaCall c = make_call(w, num, dtype, weights, grads, moms, nullptr, weights32, nullptr, nullptr, nullptr,
                         nullptr, st, dev);
   launch_fill_lrwd(c, lrs_dev, wds_dev);
@@ -479,10 +494,10 @@ int b200kv_multi_adamw_update(int num, int dtype, void* const* weights, const vo
   if (num <= 0) return 0;
   KV_CHECK(rescale_grad_dev != nullptr, "rescale_grad must be a device pointer to one float");
   const int dev = current_device();
-  OpWorkspace& w = workspace(dev);
-  std::lock_guard<std::mutex> lk(w.mu);
-  prepare_plan(w, num, sizes);
   cudaStream_t st = static_cast<cudaStream_t>(stream);
+  OpWorkspace& w = workspace(dev, stream);
+  std::lock_guard<std::mutex> lk(w.mu);
+  prepare_plan(w, num, sizes, st);
   MtaCall c = make_call(w, num, dtype, weights, grads, means, vars, weights32, lrs, wds, etas, nullptr, st, dev);
   OptScalars s;
   s.beta1 = beta1; s.beta2 = beta2; s.eps = epsilon; s.clip = clip_gradient;
@@ -496,20 +511,20 @@ int b200kv_multi_all_finite(int num, int dtype, const void* const* arrays, const
   API_BEGIN();
   if (num <= 0) return 0;
   const int dev = current_device();
-  OpWorkspace& w = workspace(dev);
-  std::lock_guard<std::mutex> lk(w.mu);
-  prepare_plan(w, num, sizes);
   cudaStream_t st = static_cast<cudaStream_t>(stream);
+  OpWorkspace& w = workspace(dev, stream);
+  std::lock_guard<std::mutex> lk(w.mu);
+  prepare_plan(w, num, sizes, st);
   KV_CHECK(dtype == kF32 || dtype == kF16, "dtype must be 0 (float32) or 2 (float16)");
   Table t{w.ring.begin(mta_blob_words(num, 1, 0) * 8), num, 1, 0};
   std::memset(t.p, 0, mta_blob_words(num, 1, 0) * 8);
   for (int i = 0; i < num; ++i) t.G(0, i, arrays[i]);
   MtaCall c;
   c.blob = w.ring.commit(st);
-  c.plan = &w.plan;
+  c.plan = w.plan;
   c.nt = num; c.ngrad = 1; c.nout = 0; c.dtype = dtype; c.stream = st; c.device = dev;
   launch_nonfinite(c, w.partials.as<float>());
-  launch_reduce_partials(w.partials.as<float>(), w.plan, 1, w.sums.as<float>(), st);
+  launch_reduce_partials(w.partials.as<float>(), *w.plan, 1, w.sums.as<float>(), st);
   launch_all_finite_final(w.sums.as<float>(), num, init_output, out, st);
   w.ring.end(st);
   API_END();
@@ -519,17 +534,17 @@ int b200kv_reset_arrays(int num, int dtype, void* const* arrays, const int64_t* 
   API_BEGIN();
   if (num <= 0) return 0;
   const int dev = current_device();
-  OpWorkspace& w = workspace(dev);
-  std::lock_guard<std::mutex> lk(w.mu);
-  prepare_plan(w, num, sizes);
   cudaStream_t st = static_cast<cudaStream_t>(stream);
+  OpWorkspace& w = workspace(dev, stream);
+  std::lock_guard<std::mutex> lk(w.mu);
+  prepare_plan(w, num, sizes, st);
   KV_CHECK(dtype == kF32 || dtype == kF16, "dtype must be 0 (float32) or 2 (float16)");
   Table t{w.ring.begin(mta_blob_words(num, 1, 1) * 8), num, 1, 1};
   std::memset(t.p, 0, mta_blob_words(num, 1, 1) * 8);
   for (int i = 0; i < num; ++i) t.G(1, i, arrays[i]);   // the out section
   MtaCall c;
   c.blob = w.ring.commit(st);
-  c.plan = &w.plan;
+  c.plan = w.plan;
   c.nt = num; c.ngrad = 1; c.nout = 1; c.dtype = dtype; c.stream = st; c.device = dev;
   launch_zero(c);
   w.ring.end(st);
@@ -541,10 +556,10 @@ int b200kv_clip_global_norm(int num, int dtype, void* const* arrays, const int64
   API_BEGIN();
   if (num <= 0) return 0;
   const int dev = current_device();
-  OpWorkspace& w = workspace(dev);
-  std::lock_guard<std::mutex> lk(w.mu);
-  prepare_plan(w, num, sizes);
   cudaStream_t st = static_cast<cudaStream_t>(stream);
+  OpWorkspace& w = workspace(dev, stream);
+  std::lock_guard<std::mutex> lk(w.mu);
+  prepare_plan(w, num, sizes, st);
   KV_CHECK(dtype == kF32 || dtype == kF16, "dtype must be 0 (float32) or 2 (float16)");
   KV_CHECK(out_scale_norm != nullptr, "out_scale_norm must point to two device floats");
   Table t{w.ring.begin(mta_blob_words(num, 1, 1) * 8), num, 1, 1};
@@ -555,11 +570,11 @@ int b200kv_clip_global_norm(int num, int dtype, void* const* arrays, const int64
   }
   MtaCall c;
   c.blob = w.ring.commit(st);
-  c.plan = &w.plan;
+  c.plan = w.plan;
   c.nt = num; c.ngrad = 1; c.nout = 1; c.dtype = dtype; c.stream = st; c.device = dev;
   float* sums = w.sums.as<float>();
   launch_sumsq(c, w.partials.as<float>());
-  launch_reduce_partials(w.partials.as<float>(), w.plan, 1, sums, st);
+  launch_reduce_partials(w.partials.as<float>(), *w.plan, 1, sums, st);
   launch_global_norm(sums, num, max_norm, out_scale_norm, st);
   launch_scale(c, out_scale_norm);
   w.ring.end(st);
@@ -571,20 +586,20 @@ int b200kv_multi_sum_sq(int num, int dtype, const void* const* arrays, const int
   API_BEGIN();
   if (num <= 0) return 0;
   const int dev = current_device();
-  OpWorkspace& w = workspace(dev);
-  std::lock_guard<std::mutex> lk(w.mu);
-  prepare_plan(w, num, sizes);
   cudaStream_t st = static_cast<cudaStream_t>(stream);
+  OpWorkspace& w = workspace(dev, stream);
+  std::lock_guard<std::mutex> lk(w.mu);
+  prepare_plan(w, num, sizes, st);
   KV_CHECK(dtype == kF32 || dtype == kF16, "dtype must be 0 (float32) or 2 (float16)");
   Table t{w.ring.begin(mta_blob_words(num, 1, 0) * 8), num, 1, 0};
   std::memset(t.p, 0, mta_blob_words(num, 1, 0) * 8);
   for (int i = 0; i < num; ++i) t.G(0, i, arrays[i]);
   MtaCall c;
   c.blob = w.ring.commit(st);
-  c.plan = &w.plan;
+  c.plan = w.plan;
   c.nt = num; c.ngrad = 1; c.nout = 0; c.dtype = dtype; c.stream = st; c.device = dev;
   launch_sumsq(c, w.partials.as<float>());
-  launch_reduce_partials(w.partials.as<float>(), w.plan, 1, out, st);
+  launch_reduce_partials(w.partials.as<float>(), *w.plan, 1, out, st);
   w.ring.end(st);
   API_END();
 }

@@ -64,6 +64,17 @@ unsigned char* scratch_on(int device) {
   return g_dev_ptr[device];
 }
 
+// SM count x resident CTAs per SM of this instantiation, capped by the chunk count: the rule
+// launch_impl.cuh's grid_for applies to the allocating entry point.
+template <class K>
+int persistent_grid(int device, int nchunks, K kernel) {
+  int per_sm = 0;
+  if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, kThreads, 0) != cudaSuccess || per_sm < 1)
+    per_sm = 2;
+  const int g = sm_count(device) * per_sm;
+  return nchunks < g ? nchunks : g;
+}
+
 }  // namespace
 
 extern "C" int b200kv_multi_sum_sq_static(int num, int dtype, const void* const* arrays,
@@ -128,13 +139,18 @@ extern "C" int b200kv_multi_sum_sq_static(int num, int dtype, const void* const*
     // Nothing in the scratch has to start at zero: stage 1 writes partials[0, c) and stage 2 reads
     // exactly that range, so whatever an earlier call left behind is never observed.
     if (c > 0) {
-      const int sms = sm_count(device) * 2;
-      const int grid = c < sms ? c : sms;
+      // Same persistent grid as b200kv_multi_sum_sq (launch_impl.cuh grid_for): the kernel carries
+      // register partials from chunk c to chunk c + gridDim of the same tensor, so the fp32
+      // summation order — and with it the last bit of the result — depends on the grid size.
+      // The occupancy query allocates nothing.
       SumSqOp op;
-      if (dtype == kF32)
+      if (dtype == kF32) {
+        const int grid = persistent_grid(device, c, mta_kernel<SumSqOp, float, float, 1>);
         mta_kernel<SumSqOp, float, float, 1><<<grid, kThreads, 0, st>>>(a, op, nullptr, partials);
-      else
+      } else {
+        const int grid = persistent_grid(device, c, mta_kernel<SumSqOp, __half, __half, 1>);
         mta_kernel<SumSqOp, __half, __half, 1><<<grid, kThreads, 0, st>>>(a, op, nullptr, partials);
+      }
       CUDA_OK(cudaGetLastError());
     }
     const int warps_per_block = 8;

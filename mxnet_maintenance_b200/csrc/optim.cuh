@@ -352,8 +352,9 @@ __device__ __forceinline__ float lamb_dir(float m, float v, float w, float wd, f
 }
 
 // pass 1: moments, and per-chunk partial sums of w^2 (in the weight dtype, multi_lamb-inl.h:286-289)
-// and u^2.  u is not stored: pass 2 recomputes it from the new m, v and the unchanged w, which
-// costs the same HBM bytes as writing and re-reading a temp_g buffer but no scratch memory.
+// and u^2.  STORE_U: u is also written to the X scratch section (the reference's temp_g) and pass
+// 2 (Lamb2UOp) streams w, u -> w; otherwise pass 2 (Lamb2Op) recomputes u from the new m, v and the
+// unchanged w — no scratch memory, more arithmetic and one more array read.
 template <bool STORE_U>
 struct Lamb1Op {
   static constexpr OpFlags F = {true, true, false, false, true, true, true, true, 2, false, STORE_U};

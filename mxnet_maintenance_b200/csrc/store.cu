@@ -482,7 +482,9 @@ void Store::run_class(Mode mode, DensePlan& p, const std::vector<const Entry*>& 
       const float* gscale = opt_.clip_global_norm >= 0.f ? global_norm_scale(p, p.full, c) : nullptr;
       update_chunks(p, p.full, c, gscale);
       prof_end();
-      s.w_stale = false;   // wbuf was written as the (fp16) out, or is the fp32 weight itself
+      // wbuf was written as the (fp16) out, or is the fp32 weight itself — for THESE keys only: an
+      // earlier non-aliased multi-precision push may have left other keys of the segment stale
+      if (p.full_segment) s.w_stale = false;
       ring_.end(stream_);
       return;
     }
@@ -1156,9 +1158,24 @@ void Store::set_state(int key, int which, DLManagedTensor* in) {
                             static_cast<size_t>(hi - lo) * 4, cudaMemcpyDeviceToDevice, stream_));
   if (which == 2) {
     // the fp16 stored value follows its master
-    if (world_ == 1) s.w_stale = true;
-    else if (lo < hi)
-      launches_ += launch_cast(at(*dst, lo - s.state_begin, 4), kF32, at(s.wbuf, lo, 2), kF16, hi - lo, stream_);
+    if (world_ == 1) {
+      s.w_stale = true;
+    } else {
+      if (lo < hi)
+        launches_ += launch_cast(at(*dst, lo - s.state_begin, 4), kF32, at(s.wbuf, lo, 2), kF16, hi - lo, stream_);
+      // every rank refreshed only its own shard of the fp16 value: exchange the pieces so that a
+      // pull before the next push returns the loaded weights everywhere
+      KV_CHECK(comm_, "b200kv_comm_init has not been called");
+      NcclApi& nccl = NcclApi::get();
+      NCCL_OK(nccl.GroupStart());
+      for (int r = 0; r < world_; ++r) {
+        const int64_t plo = std::max(ki.off, r * s.slice), phi = std::min(ki.off + ki.size, (r + 1) * s.slice);
+        if (plo < phi)
+          NCCL_OK(nccl.Broadcast(at(s.wbuf, plo, 2), at(s.wbuf, plo, 2), phi - plo, ncclFloat16, r,
+                                 reinterpret_cast<ncclComm_t>(comm_), stream_));
+      }
+      NCCL_OK(nccl.GroupEnd());
+    }
   }
 }
 

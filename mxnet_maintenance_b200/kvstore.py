@@ -18,7 +18,7 @@ import os
 
 from . import _lib
 from ._lib import B200KVError, OptimizerDesc, check_call
-from .base import KVStoreBase, HAVE_MXNET
+from ._mx_shim import KVStoreBase, HAVE_MXNET
 from .dlpack import HandleCache
 from . import optimizer as opt_mod
 
@@ -202,6 +202,7 @@ class B200(KVStoreBase):
         self._rsp_shapes = {}
         self._dense_keys = []
         self._sizes = {}
+        self._shapes = {}
         self.clip_global_norm = None
         # auto_batch: gluon.Trainer issues one pushpull PER PARAMETER (trainer.py:392-395).  With
         # auto_batch the per-key calls are only recorded; once every dense key of the store has
@@ -363,6 +364,7 @@ class B200(KVStoreBase):
             for i in dense_idx:
                 self._dense_keys.append(keys[i])
                 self._sizes[keys[i]] = _numel(vals[i])
+                self._shapes[keys[i]] = tuple(vals[i].shape)
 
     def push(self, key, value, priority=0):
         """kvstore.py:178-270."""
@@ -535,6 +537,7 @@ class B200(KVStoreBase):
         for k, v in zip(vkeys, vals):
             self._dense_keys.append(k)
             self._sizes[k] = _numel(v)
+            self._shapes[k] = tuple(v.shape)
 
     # ------------------------------------------------------------------ row sparse
     def _init_rsp(self, ckey, v, key):
@@ -688,18 +691,7 @@ class B200(KVStoreBase):
         kind = opt_mod.kind_of(self._updater.optimizer)
         states = {}
         for key in dict.fromkeys(self._dense_keys):
-            ck = self._keys([key], isinstance(key, str))
-            got = []
-            for which in (0, 1, 2):
-                n = self._key_size(key)
-                buf = _empty((n,), "float32", self._device)
-                p, keep = self._handles([buf], True)
-                present = C.c_int()
-                check_call(self._lib.b200kv_get_state(self._h, ck[0], which, p[0], C.byref(present)))
-                if present.value:
-                    check_call(self._lib.b200kv_wait(self._h))
-                got.append(_to_numpy(buf) if present.value else None)
-            s0, s1, w32 = got
+            s0, s1, w32 = [self.get_state(key, which) for which in (0, 1, 2)]
             if s0 is None and s1 is None and w32 is None and kind != "sgd":
                 continue
             if kind == "sgd":
@@ -721,8 +713,20 @@ class B200(KVStoreBase):
         self._updater.states = states
         return states
 
-    def _key_size(self, key):
-        return self._sizes[key]
+    def get_state(self, key, which):
+        """One optimizer-state array of `key` as numpy, shaped like the weight (the reference creates
+        states with zeros(weight.shape), optimizer.py:583-600,1602-1607), or None when the current
+        optimizer keeps no such state.  which: 0 momentum | mean | history, 1 var, 2 fp32 master.
+        Collective when num_workers > 1 (the state is sharded across ranks)."""
+        ck = self._keys([key], isinstance(key, str))
+        buf = _empty((self._sizes[key],), "float32", self._device)
+        p, keep = self._handles([buf], True)
+        present = C.c_int()
+        check_call(self._lib.b200kv_get_state(self._h, ck[0], which, p[0], C.byref(present)))
+        if not present.value:
+            return None
+        check_call(self._lib.b200kv_wait(self._h))
+        return _to_numpy(buf).reshape(self._shapes[key])
 
     def save_optimizer_states(self, fname, dump_optimizer=False):
         """kvstore.py:641-666."""

@@ -321,6 +321,20 @@ class LocalStoreModel:
     def pull(self, key):
         return self.store[key].copy()
 
+    def states_of(self, key):
+        """{which: flat fp32 array} in the store's numbering (b200kv_get_state): 0 momentum | mean |
+        AdaGrad history, 1 var, 2 fp32 master weight."""
+        st, kind = self.state.get(key), (self.opt or {}).get("kind")
+        if st is None:
+            return {}
+        if kind == "sgd":
+            d = {0: st[0], 2: st[1]}
+        elif kind == "adagrad":
+            d = {0: st[1], 2: st[0]}
+        else:
+            d = {0: st[1], 1: st[2], 2: st[0]}
+        return {k: v for k, v in d.items() if v is not None}
+
     def pushpull(self, key, values):
         self.push(key, values)
         return self.pull(key)

@@ -1,6 +1,7 @@
-"""Pure-Python statement of the store's flat-segment layout and shard ownership (csrc/store.cu:
-``Store::seal`` / ``Store::plan_for``), used by tools that need to know which rank owns which
-elements (checkpoint re-sharding, the multi-rank tests) without a GPU.
+"""TEST HELPER (not product code): pure-Python statement of the store's flat-segment layout and
+shard ownership (csrc/store.cu ``Store::seal`` / ``Store::plan_for``).  The gloo tests use it to
+shard a CPU update the way the store would; tests/test_dense_gpu.py::test_layout_planner_matches_store
+pins it against the real store through the addresses of ``b200kv_view``.
 
 Layout rule: keys are laid out in init order, each starting on a 64-element boundary; the segment
 is padded to a multiple of ``world * 64`` elements and rank r owns ``[r*slice, (r+1)*slice)``.

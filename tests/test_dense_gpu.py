@@ -81,6 +81,15 @@ def _run(oracle, shape_name, opt_kind, ncopies, steps=3, mp=False, clip=None, gc
         else:
             ref = [model.pushpull(k, grads[k]) for k in keys]
         got = [w.cpu().numpy() for w in dev_w]
+        if step == steps - 1 and opt is not None:
+            # "weights AND optimizer states" (north star): every state array the reference keeps
+            # (momentum | mean, var | history, fp32 master) is compared like one more key
+            for k in keys:
+                for which, want in sorted(model.states_of(k).items()):
+                    have = kv.get_state(k, which)
+                    assert have is not None, "key %d: state %d missing in the store" % (k, which)
+                    got.append(have.reshape(-1))
+                    ref.append(want)
         results.append((got, ref))
     return kv, model, results
 
@@ -478,3 +487,22 @@ def test_no_out_of_bounds_writes(kind, dt):
                 assert torch.allclose(a.float(), b.float(), rtol=2e-3 if mp else 1e-5, atol=1e-6)
             else:
                 assert torch.equal(a, b)
+
+
+def test_layout_planner_matches_store():
+    """tests/layout_planner.py (used by the gloo tests to shard a CPU update like the store does) against
+    the REAL layout: element offsets of every key inside its segment, read back through the
+    addresses of the store's own views (b200kv_view)."""
+    import layout_planner
+    mb = _mb()
+    shp = _shapes("ragged") + _shapes("mlp")
+    kv = mb.create("b200")
+    keys = list(range(len(shp)))
+    kv.init(keys, [torch.zeros(s, device="cuda") for s in shp])
+    sizes = [int(np.prod(s)) for s in shp]
+    offs, total, sl = layout_planner.segment_layout(sizes, 1)
+    seg_w, seg_g = kv.segment_views(0)
+    assert seg_w.numel() == total == sl
+    for k, o in zip(keys, offs):
+        assert (kv.weight_view(k).data_ptr() - seg_w.data_ptr()) // 4 == o
+        assert (kv.grad_view(k).data_ptr() - seg_g.data_ptr()) // 4 == o

@@ -164,10 +164,10 @@ def test_save_load_optimizer_states(tmp_path, kind, mp):
     def make():
         kv = m.create("b200")
         kv.set_optimizer(O(learning_rate=0.01, multi_precision=mp, **kw))
-        w = [torch.linspace(-1, 1, 100, device="cuda").to(dt), torch.linspace(0, 1, 7, device="cuda").to(dt)]
+        w = [torch.linspace(-1, 1, 100, device="cuda").to(dt).view(10, 10), torch.linspace(0, 1, 7, device="cuda").to(dt)]
         kv.broadcast([0, 1], w, out=[[x] for x in w])
         return kv, w
-    g = [torch.full((100,), 0.01, device="cuda").to(dt), torch.full((7,), -0.02, device="cuda").to(dt)]
+    g = [torch.full((10, 10), 0.01, device="cuda").to(dt), torch.full((7,), -0.02, device="cuda").to(dt)]
     kv1, w1 = make()
     for _ in range(2):
         kv1.pushpull([0, 1], g, out=[[x] for x in w1])
@@ -175,10 +175,15 @@ def test_save_load_optimizer_states(tmp_path, kind, mp):
     kv1.save_optimizer_states(f, dump_optimizer=True)
     states, opt = pickle.loads(open(f, "rb").read())
     st = states[0]
+    # every state array has the WEIGHT's shape (zeros(weight.shape), optimizer.py:583-600,1602-1607),
+    # so a native store / Trainer can load the file
     if kind == "sgd":
-        assert (isinstance(st, tuple) and len(st) == 2 and st[1].dtype == np.float32) if mp else st.shape == (100,)
+        assert (isinstance(st, tuple) and len(st) == 2 and st[1].dtype == np.float32 and
+                st[0].shape == (10, 10) and st[1].shape == (10, 10)) if mp else st.shape == (10, 10)
     else:
-        assert isinstance(st[1], tuple) if mp else (len(st) == 2 and st[0].shape == (100,))
+        assert (isinstance(st[1], tuple) and st[0].shape == (10, 10) and st[1][0].shape == (10, 10)) if mp \
+            else (len(st) == 2 and st[0].shape == (10, 10) and st[1].shape == (10, 10))
+    assert states[1].shape == (7,) if (kind == "sgd" and not mp) else True
     assert opt.num_update == 2
     # continue in a fresh store from the checkpoint == continue in the original
     kv2, w2 = make()

@@ -18,9 +18,11 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
 def _worker(rank, world, port, q):
     sys.path.insert(0, ROOT)
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
     os.environ["MASTER_ADDR"], os.environ["MASTER_PORT"] = "127.0.0.1", str(port)
     dist.init_process_group("gloo", rank=rank, world_size=world)
-    from mxnet_maintenance_b200 import planner, shapes
+    from mxnet_maintenance_b200 import shapes
+    import layout_planner as planner
     from oracle.oracle import Oracle
     o = Oracle("port", nthread=1)
     shp = shapes.mlp() + [(1,), (63,), (65,), (4097,)]
@@ -86,7 +88,8 @@ def test_two_rank_host_logic():
 
 
 def test_planner_matches_store_rules():
-    from mxnet_maintenance_b200 import planner
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import layout_planner as planner
     offs, total, sl = planner.segment_layout([1, 64, 65, 1000], 8)
     assert offs == [0, 64, 128, 256] and total % (8 * 64) == 0 and sl * 8 == total
     assert planner.segment_layout([], 2)[1] == 128

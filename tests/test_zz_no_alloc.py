@@ -4,7 +4,9 @@ synchronisation of cudaMalloc is unacceptable).  It works inside one fixed array
 the library image, so here it is driven straight through the C ABI and compared with the regular,
 allocating b200kv_multi_sum_sq on the same inputs.  Both run the same deterministic kernels, so
 the comparison is exact (tolerance 0), on two calls in a row: the second call uses fewer and
-smaller arrays, so it runs on top of whatever the first call left in the shared array.
+smaller arrays, so it runs on top of whatever the first call left in the shared array.  One array
+is larger than a whole persistent grid's worth of chunks (5 M elements), where the order of the
+fp32 additions depends on the grid size — both entry points must size their grids alike.
 
 This file sorts last on purpose: a `-x` run has already executed every other test before it."""
 import ctypes as C
@@ -39,7 +41,7 @@ def test_static_sum_sq_matches_allocating_entry_point_twice(dtype):
     lib = _lib.load()
     gen = torch.Generator(device="cuda").manual_seed(5)
     first = [torch.randn(s, device="cuda", generator=gen).to(dtype)
-             for s in (1, 3, 4095, 4096, 4097, 100003, 0, 1 << 20, 777, 65536)]
+             for s in (1, 3, 4095, 4096, 4097, 100003, 0, 1 << 20, 777, 65536, 5_000_011)]
     second = [torch.randn(s, device="cuda", generator=gen).to(dtype) for s in (5000, 2, 8193)]
     for arrays in (first, second):
         ref, got = _pair(lib, arrays)

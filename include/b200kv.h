@@ -210,6 +210,11 @@ int b200kv_profile_read(b200kv_handle h, double* kernel_ms, int64_t* count);
  * broadcast, [4] unpack (the reference names these engine ops "KVStoreReduce", "KVStoreBCast", …,
  * src/kvstore/comm.h:171,264; kvstore_nccl.h:316,420) */
 int b200kv_profile_read_phases(b200kv_handle h, double ms[8], int64_t count[8]);
+/* which mechanism carried the cross-GPU exchange of the last dense push: "local" (one GPU, nothing
+ * exchanged), "peer" (fused kernel over NVLink peer memory), "peer-push", "nvls" (fused kernel over
+ * the NVSwitch multicast mapping) or "nccl" (ncclReduceScatter / ncclAllGather).  Reporting only
+ * (the reference exposes its choice through the store type string, src/kvstore/kvstore.cc:41-82). */
+int b200kv_last_exchange(b200kv_handle h, const char** out);
 /* number of kernels this store has launched so far (bench.py's gpu_launches) */
 int b200kv_launch_count(b200kv_handle h, int64_t* out);
 

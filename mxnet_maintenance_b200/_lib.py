@@ -68,6 +68,7 @@ SIGNATURES = {
     "b200kv_get_rank": [_VP, _PI],
     "b200kv_get_group_size": [_VP, _PI],
     "b200kv_barrier": [_VP],
+    "b200kv_last_exchange": [_VP, C.POINTER(C.c_char_p)],
     "b200kv_launch_count": [_VP, C.POINTER(_I64)],
     "b200kv_multi_sgd_update": [_I, _I, _PVP, _PVP, _PVP, _PVP, C.POINTER(_I64), _PF, _PF, _F, _F,
                                 _F, _VP],

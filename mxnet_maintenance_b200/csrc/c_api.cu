@@ -262,6 +262,12 @@ int b200kv_barrier(b200kv_handle h) {
   API_END();
 }
 
+int b200kv_last_exchange(b200kv_handle h, const char** out) {
+  API_BEGIN();
+  *out = S(h)->last_exchange();
+  API_END();
+}
+
 int b200kv_launch_count(b200kv_handle h, int64_t* out) {
   API_BEGIN();
   *out = S(h)->launches();

@@ -528,6 +528,7 @@ void Store::run_class(Mode mode, DensePlan& p, const std::vector<const Entry*>& 
   }
 
   // ---------------- world > 1: pack -> reduce-scatter -> sharded update -> all-gather -> unpack
+  if (push) last_exchange_ = "nccl";
   if (s.gbuf.p == nullptr && push) alloc_gbuf(s);
   if (push && has_opt() && p.full_segment) {
     if (!s.p2p.tried) setup_p2p(s);
@@ -799,6 +800,7 @@ void Store::run_class_p2p(DensePlan& p, Segment& s, const std::vector<const Entr
     if (k == rank_) return static_cast<const char*>(s.gbuf.p) + off * es;
     return static_cast<const char*>(P.local_stage.p) + (static_cast<int64_t>(k) * s.slice + off - rank_ * s.slice) * es;
   };
+  last_exchange_ = nvls ? "nvls" : (push_rs ? "peer-push" : "peer");
   const int pre_ng = nvls ? 1 : W;
   const int upd_ng = (prereduce || nvls) ? 1 : W, upd_no = nvls ? 1 : (mp ? W : W - 1);
   const size_t w_pack = mta_blob_words(nt, ng, 0), w_pre = prereduce ? mta_blob_words(nt, pre_ng, 0) : 0,

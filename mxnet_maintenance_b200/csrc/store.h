@@ -120,6 +120,7 @@ class Store {
   int world() const { return world_; }
   int64_t launches() const { return launches_; }
   const char* type() const { return "b200"; }
+  const char* last_exchange() const { return last_exchange_; }
 
  private:
   friend struct RspKey;
@@ -178,6 +179,7 @@ class Store {
   DevBuf gnorm_;           // float[2]: scale, norm of the last clipped push
   bool gnorm_valid_ = false;
   int64_t launches_ = 0;
+  const char* last_exchange_ = "local";
   b200kv_symm_alloc_fn symm_alloc_ = nullptr;
   void* symm_ctx_ = nullptr;
   std::unordered_map<int, std::unique_ptr<BoundCall>> bound_;

@@ -676,6 +676,12 @@ class B200(KVStoreBase):
         check_call(self._lib.b200kv_launch_count(self._h, C.byref(n)))
         return n.value
 
+    def last_exchange(self):
+        """'local' | 'peer' | 'peer-push' | 'nvls' | 'nccl': what carried the last dense push across GPUs."""
+        p = C.c_char_p()
+        check_call(self._lib.b200kv_last_exchange(self._h, C.byref(p)))
+        return p.value.decode()
+
     def last_global_norm(self):
         v = C.c_float()
         check_call(self._lib.b200kv_last_global_norm(self._h, C.byref(v)))

@@ -8,7 +8,7 @@ import ctypes as C
 import os
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, "libb200kv.so")
+LIB_PATH = os.environ.get("B200KV_LIB") or os.path.join(HERE, "libb200kv.so")   # B200KV_LIB: A/B builds
 
 
 class B200KVError(RuntimeError):

@@ -20,6 +20,7 @@ namespace b200kv {
 
 constexpr int kU = 4;  // 128-bit vectors per thread per chunk
 
+
 // ------------------------------------------------------------------------------------------------
 // element-type helpers
 // ------------------------------------------------------------------------------------------------
@@ -50,6 +51,31 @@ __device__ __forceinline__ float ld1(const __half* p) { return __half2float(*p);
 __device__ __forceinline__ void st1(float* p, float v) { *p = v; }
 __device__ __forceinline__ void st1(__half* p, float v) { *p = __float2half_rn(v); }
 
+// A 4-element vector as it comes out of memory.  The kernel issues ALL loads of an iteration into
+// these before the first conversion or addition touches one, so every load of a thread is in flight
+// at once (an fp16 load followed directly by its half->float conversion would stall the next load
+// behind a full DRAM round trip).
+template <typename T> struct Raw;
+template <> struct Raw<float> { float4 v; };
+template <> struct Raw<__half> { uint2 v; };
+// (Measured, round 2: telling the compiler these pointers are global — __builtin_assume(__isGlobal(p)),
+// which turns the generic LD.E.128 / ST.E.128 into LDG / STG — made the fp32 SGD kernel 30% SLOWER on
+// B200 (0.109 vs 0.083 ms on ResNet-50), so the accesses stay generic.)
+__device__ __forceinline__ void ldraw(const float* p, Raw<float>& r) {
+  r.v = *reinterpret_cast<const float4*>(p);
+}
+__device__ __forceinline__ void ldraw(const __half* p, Raw<__half>& r) {
+  r.v = *reinterpret_cast<const uint2*>(p);
+}
+__device__ __forceinline__ void cvt(const Raw<float>& r, float (&v)[4]) {
+  v[0] = r.v.x; v[1] = r.v.y; v[2] = r.v.z; v[3] = r.v.w;
+}
+__device__ __forceinline__ void cvt(const Raw<__half>& r, float (&v)[4]) {
+  const float2 a = __half22float2(*reinterpret_cast<const __half2*>(&r.v.x));
+  const float2 b = __half22float2(*reinterpret_cast<const __half2*>(&r.v.y));
+  v[0] = a.x; v[1] = a.y; v[2] = b.x; v[3] = b.y;
+}
+
 // NVLS (NVLink SHARP): a load from a MULTICAST address returns the sum of that element over every
 // GPU bound to the multicast object, reduced inside the NVSwitch; a store to it lands on every GPU.
 // One such load replaces W-1 peer loads (the reduce-scatter half), one such store W-1 peer stores
@@ -60,23 +86,9 @@ __device__ __forceinline__ void mc_ld4(const float* p, float (&v)[4]) {
   asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0,%1,%2,%3}, [%4];"
                : "=f"(v[0]), "=f"(v[1]), "=f"(v[2]), "=f"(v[3]) : "l"(p) : "memory");
 }
-__device__ __forceinline__ void mc_ld4(const __half* p, float (&v)[4]) {
-  uint32_t a, b;
-  asm volatile("multimem.ld_reduce.relaxed.sys.global.add.acc::f32.v2.f16x2 {%0,%1}, [%2];"
-               : "=r"(a), "=r"(b) : "l"(p) : "memory");
-  const float2 x = __half22float2(*reinterpret_cast<const __half2*>(&a));
-  const float2 y = __half22float2(*reinterpret_cast<const __half2*>(&b));
-  v[0] = x.x; v[1] = x.y; v[2] = y.x; v[3] = y.y;
-}
 __device__ __forceinline__ void mc_st4(float* p, const float (&v)[4]) {
   asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(p), "f"(v[0]), "f"(v[1]),
                "f"(v[2]), "f"(v[3]) : "memory");
-}
-__device__ __forceinline__ void mc_st4(__half* p, const float (&v)[4]) {
-  const __half2 a = __floats2half2_rn(v[0], v[1]);
-  const __half2 b = __floats2half2_rn(v[2], v[3]);
-  asm volatile("multimem.st.relaxed.sys.global.v2.f16x2 [%0], {%1,%2};" ::"l"(p),
-               "r"(*reinterpret_cast<const uint32_t*>(&a)), "r"(*reinterpret_cast<const uint32_t*>(&b)) : "memory");
 }
 __device__ __forceinline__ float mc_ld1(const float* p) {
   float v;
@@ -86,10 +98,8 @@ __device__ __forceinline__ float mc_ld1(const float* p) {
 __device__ __forceinline__ void mc_st1(float* p, float v) {
   asm volatile("multimem.st.relaxed.sys.global.f32 [%0], %1;" ::"l"(p), "f"(v) : "memory");
 }
-// There is no scalar f16 multimem form: the store rounds multicast chunks up to whole 4-element
-// vectors (inside the zero padding of a 64-element bucket slot), so fp16 never takes this path.
-__device__ __forceinline__ float mc_ld1(const __half*) { __trap(); return 0.f; }
-__device__ __forceinline__ void mc_st1(__half*, float) { __trap(); }
+// fp16 buckets never take the multicast path (the switch's half additions round differently from the
+// reference's): fp16 kernels are compiled without any multimem code.
 
 // value of x after a round trip through the tensor's element type
 template <typename T> __device__ __forceinline__ float round_to(float x);
@@ -124,12 +134,32 @@ __device__ __forceinline__ const uint64_t* sec(const MtaArgs& a, int s) {
 // loads of a vector are in flight together without blowing the register budget
 template <int NG> struct Unroll { static constexpr int value = NG <= 2 ? 4 : (NG <= 4 ? 2 : 1); };
 
+// phase 1: issue the loads of every gradient copy of one vector (nothing is converted or added yet)
 template <typename T, int NG>
-__device__ __forceinline__ void grad4(const MtaArgs& a, const T* const* gp, int t, int64_t e,
-                                      float (&g)[4]) {
+__device__ __forceinline__ void grad_load(const MtaArgs& a, const T* const* gp, int64_t e,
+                                          Raw<T> (&r)[NG > 0 ? NG : 1]) {
   if constexpr (NG == 1) {
-    if (a.sync_mode & kSyncMcGrad) mc_ld4(gp[0] + e, g);
-    else ld4(gp[0] + e, g);
+    if constexpr (sizeof(T) == 4) {   // NVLS is fp32 only: fp16 kernels carry no multimem code at all
+      if (a.sync_mode & kSyncMcGrad) {
+        float v[4];
+        mc_ld4(gp[0] + e, v);
+        r[0].v = make_float4(v[0], v[1], v[2], v[3]);
+        return;
+      }
+    }
+    ldraw(gp[0] + e, r[0]);
+  } else if constexpr (NG > 1) {
+    // all NG loads (local or NVLink peer memory) are issued back to back
+#pragma unroll
+    for (int k = 0; k < NG; ++k) ldraw(gp[k] + e, r[k]);
+  }
+}
+// phase 2: convert and sum in CommCPU order
+template <typename T, int NG>
+__device__ __forceinline__ void grad_finish(const MtaArgs& a, int t, int64_t e,
+                                            const Raw<T> (&r)[NG > 0 ? NG : 1], float (&g)[4]) {
+  if constexpr (NG == 1) {
+    cvt(r[0], g);
   } else if constexpr (NG == 0) {
     ld4(reinterpret_cast<const T*>(sec_grad(a, 0)[t]) + e, g);
     for (int i = 1; i < a.ngrad; i += 4) {
@@ -145,10 +175,9 @@ __device__ __forceinline__ void grad4(const MtaArgs& a, const T* const* gp, int 
       for (int j = 0; j < 4; ++j) g[j] = add_as<T>(g[j], s[j]);
     }
   } else {
-    // all NG loads (local or NVLink peer memory) are issued back to back, then summed in order
     float x[NG][4];
 #pragma unroll
-    for (int k = 0; k < NG; ++k) ld4(gp[k] + e, x[k]);
+    for (int k = 0; k < NG; ++k) cvt(r[k], x[k]);
 #pragma unroll
     for (int j = 0; j < 4; ++j) {
       float acc = x[0][j];
@@ -166,7 +195,9 @@ __device__ __forceinline__ void grad4(const MtaArgs& a, const T* const* gp, int 
 }
 template <typename T, int NG>
 __device__ __forceinline__ float grad1(const MtaArgs& a, int t, int64_t e) {
-  if (NG == 1 && (a.sync_mode & kSyncMcGrad)) return mc_ld1(reinterpret_cast<const T*>(sec_grad(a, 0)[t]) + e);
+  if constexpr (NG == 1 && sizeof(T) == 4) {
+    if (a.sync_mode & kSyncMcGrad) return mc_ld1(reinterpret_cast<const T*>(sec_grad(a, 0)[t]) + e);
+  }
   float g = ld1(reinterpret_cast<const T*>(sec_grad(a, 0)[t]) + e);
   if (NG != 1) {
     for (int i = 1; i < a.ngrad; i += 4) {
@@ -546,14 +577,16 @@ mta_kernel(const MtaArgs a, const Op op, const float* __restrict__ gscale,
       constexpr int U = Unroll<NG>::value;
       for (int v0 = 0; v0 < nvec; v0 += U * kThreads) {
       float w[U][4], g[U][4], s0[U][4], s1[U][4], x[U][4];
+      Raw<T> gr[U][NGC];
+      Raw<WT> wr[U];
 #pragma unroll
       for (int u = 0; u < U; ++u) {
         const int v = v0 + u * kThreads + tid;
         if (v < nvec) {
           const int64_t e = base + 4 * v;
           if (F.read_x) ld4(xp + e, x[u]);
-          if (F.read_g) grad4<T, NG>(a, gp, t, e, g[u]);
-          if (F.read_w) ld4(wp + e, w[u]);
+          if (F.read_g) grad_load<T, NG>(a, gp, e, gr[u]);
+          if (F.read_w) ldraw(wp + e, wr[u]);
           if (F.read_s0) ld4(s0p + e, s0[u]);
           if (F.read_s1) ld4(s1p + e, s1[u]);
         }
@@ -563,6 +596,8 @@ mta_kernel(const MtaArgs a, const Op op, const float* __restrict__ gscale,
         const int v = v0 + u * kThreads + tid;
         if (v < nvec) {
           const int64_t e = base + 4 * v;
+          if (F.read_g) grad_finish<T, NG>(a, t, e, gr[u], g[u]);
+          if (F.read_w) cvt(wr[u], w[u]);
 #pragma unroll
           for (int j = 0; j < 4; ++j) {
             if (use_gs) g[u][j] = round_to<T>(__fmul_rn(g[u][j], gs));
@@ -575,8 +610,13 @@ mta_kernel(const MtaArgs a, const Op op, const float* __restrict__ gscale,
           if (F.write_s1) st4(s1p + e, s1[u]);
           if (F.write_w) st4(wp + e, w[u]);
           if (F.write_out) {
-            if (a.sync_mode & kSyncMcOut) mc_st4(reinterpret_cast<T*>(sec_out(a, 0)[t]) + e, w[u]);
-            else for (int k = 0; k < a.nout; ++k) st4(reinterpret_cast<T*>(sec_out(a, k)[t]) + e, w[u]);
+            bool mc = false;
+            if constexpr (sizeof(T) == 4) {
+              mc = (a.sync_mode & kSyncMcOut) != 0;
+              if (mc) mc_st4(reinterpret_cast<T*>(sec_out(a, 0)[t]) + e, w[u]);
+            }
+            if (!mc)
+              for (int k = 0; k < a.nout; ++k) st4(reinterpret_cast<T*>(sec_out(a, k)[t]) + e, w[u]);
           }
         }
       }
@@ -598,8 +638,13 @@ mta_kernel(const MtaArgs a, const Op op, const float* __restrict__ gscale,
       if (F.write_s1) s1p[e] = s1;
       if (F.write_w) st1(wp + e, w);
       if (F.write_out) {
-        if (a.sync_mode & kSyncMcOut) mc_st1(reinterpret_cast<T*>(sec_out(a, 0)[t]) + e, w);
-        else for (int k = 0; k < a.nout; ++k) st1(reinterpret_cast<T*>(sec_out(a, k)[t]) + e, w);
+        bool mc = false;
+        if constexpr (sizeof(T) == 4) {
+          mc = (a.sync_mode & kSyncMcOut) != 0;
+          if (mc) mc_st1(reinterpret_cast<T*>(sec_out(a, 0)[t]) + e, w);
+        }
+        if (!mc)
+          for (int k = 0; k < a.nout; ++k) st1(reinterpret_cast<T*>(sec_out(a, k)[t]) + e, w);
       }
     }
 

@@ -11,10 +11,12 @@
  * BORROWED for the duration of the call: the library never calls `deleter` and never frees caller
  * memory.  Tensors must be compact row-major CUDA tensors on the store's device.
  *
- * One store drives ONE GPU; several processes (one per GPU) form a communicator
- * (b200kv_comm_unique_id / b200kv_comm_init).  Within a process a key may be pushed as several
- * device-local copies (the reference's "one value per device" lists); they are summed in the
- * reference's CommCPU order before the cross-GPU reduction.
+ * Two ways to drive several GPUs: b200kv_create makes a store for ONE GPU and several processes
+ * (one per GPU) form a communicator (b200kv_comm_unique_id / b200kv_comm_init); b200kv_create_group
+ * makes ONE store that drives several GPUs from one process, the way the reference's 'device' and
+ * 'nccl' stores do.  On one GPU a key may be pushed as several device-local copies (the reference's
+ * "one value per device" lists); they are summed in the reference's CommCPU order before the
+ * cross-GPU reduction.
  *
  * All work is enqueued on the stream given to b200kv_set_stream (default: the legacy default
  * stream, which orders with MXNet's blocking streams); b200kv_wait blocks until it has drained.
@@ -68,6 +70,31 @@ int b200kv_version(int* out);
  * device_id: CUDA ordinal this store drives.  rank/world_size: position among the cooperating
  * processes (MXKVStoreGetRank / MXKVStoreGetGroupSize). */
 int b200kv_create(int device_id, int rank, int world_size, b200kv_handle* out);
+/* The reference's own usage model: ONE process driving several GPUs — mx.kv.create('device' / 'nccl')
+ * holds one NDArray per device (CommDevice::Reduce / Broadcast / InitMergeBuffer / EnableP2P,
+ * src/kvstore/comm.h:503-616,678-757; KVStoreNCCL::InitNCCL = ncclCommInitAll,
+ * src/kvstore/kvstore_nccl.h:475-493) and gluon.Trainer hands param.list_grad() / list_data() — one
+ * array per context — to every pushpull (python/mxnet/gluon/trainer.py:392-395).
+ * The handle is used with the SAME entry points as a single-GPU store: for every key the value list
+ * of push / pushpull must hold (at least) one array per device of the group, outs may name any of
+ * them; an array is routed by the device it lives on.  The devices must have peer access to each
+ * other (NVLink / NVSwitch): the members exchange through peer memory with the same fused
+ * reduce-scatter + update + all-gather kernel as the one-process-per-GPU mode, one launch per device,
+ * ordered on the GPUs by flag barriers; no NCCL communicator and no IPC mapping is involved.
+ * Optimizer state is sharded over the devices (state memory / ndev).  A device may be listed several
+ * times ("virtual ranks": the copies of a key on that GPU are dealt to its members in list order) —
+ * that runs the full multi-rank path on one GPU and is what the single-GPU tests use.
+ * MXKVStoreGetRank / GetGroupSize report 0 / 1: a group is ONE worker. */
+int b200kv_create_group(int ndev, const int* dev_ids, b200kv_handle* out);
+/* number of members (devices) of a group handle; 1 for a single-GPU store */
+int b200kv_group_size(b200kv_handle h, int* out);
+/* the caller's stream on each member's device (cudaStream_t, one per member, in dev_ids order): the
+ * group's work is ordered after what these streams hold at the time of a call, and they are made to
+ * wait for it.  Default: the legacy default stream of each device.  (b200kv_set_stream is the
+ * single-GPU form.) */
+int b200kv_group_set_streams(b200kv_handle h, int n, void* const* streams);
+/* b200kv_view for member `member` of a group (b200kv_view on a group handle means member 0) */
+int b200kv_group_view(b200kv_handle h, int member, int key, int which, DLManagedTensor** out);
 /* MXKVStoreFree (c_api.h:2740) */
 int b200kv_free(b200kv_handle h);
 /* stream all subsequent work is enqueued on (a cudaStream_t passed as an integer/pointer) */

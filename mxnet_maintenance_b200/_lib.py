@@ -35,6 +35,10 @@ _PVP = C.POINTER(C.c_void_p)
 SIGNATURES = {
     "b200kv_version": [_PI],
     "b200kv_create": [_I, _I, _I, _PVP],
+    "b200kv_create_group": [_I, _PI, _PVP],
+    "b200kv_group_size": [_VP, _PI],
+    "b200kv_group_set_streams": [_VP, _I, _PVP],
+    "b200kv_group_view": [_VP, _I, _I, _I, _PVP],
     "b200kv_free": [_VP],
     "b200kv_set_stream": [_VP, _VP],
     "b200kv_wait": [_VP],

@@ -7,6 +7,7 @@
 #include <mutex>
 #include <vector>
 
+#include "group.h"
 #include "nccl_dl.h"
 #include "store.h"
 
@@ -29,10 +30,31 @@ using namespace b200kv;
   }                                                 \
   return 0;
 
-static Store* S(b200kv_handle h) {
+static KVHandle* H(b200kv_handle h) {
   KV_CHECK(h != nullptr, "null store handle");
-  return static_cast<Store*>(h);
+  return static_cast<KVHandle*>(h);
 }
+static Store* S(b200kv_handle h) {
+  KVHandle* b = H(h);
+  KV_CHECK(!b->is_group, "this entry point needs a single-GPU store handle, got a group handle");
+  return static_cast<Store*>(b);
+}
+static Group* G(b200kv_handle h) {
+  KVHandle* b = H(h);
+  KV_CHECK(b->is_group, "this entry point needs a handle made by b200kv_create_group");
+  return static_cast<Group*>(b);
+}
+// the same call on whichever object the handle is
+#define KV(h, call)                                      \
+  do {                                                   \
+    if (H(h)->is_group) static_cast<Group*>(H(h))->call; \
+    else static_cast<Store*>(H(h))->call;                \
+  } while (0)
+#define KVR(h, lhs, call)                                      \
+  do {                                                         \
+    if (H(h)->is_group) lhs = static_cast<Group*>(H(h))->call; \
+    else lhs = static_cast<Store*>(H(h))->call;                \
+  } while (0)
 
 extern "C" {
 
@@ -46,13 +68,38 @@ int b200kv_version(int* out) {
 
 int b200kv_create(int device_id, int rank, int world_size, b200kv_handle* out) {
   API_BEGIN();
-  *out = new Store(device_id, rank, world_size);
+  *out = static_cast<KVHandle*>(new Store(device_id, rank, world_size));
+  API_END();
+}
+
+int b200kv_create_group(int ndev, const int* dev_ids, b200kv_handle* out) {
+  API_BEGIN();
+  KV_CHECK(dev_ids != nullptr && out != nullptr, "null argument");
+  *out = static_cast<KVHandle*>(new Group(ndev, dev_ids));
+  API_END();
+}
+
+int b200kv_group_set_streams(b200kv_handle h, int n, void* const* streams) {
+  API_BEGIN();
+  G(h)->set_streams(n, streams);
+  API_END();
+}
+
+int b200kv_group_view(b200kv_handle h, int member, int key, int which, DLManagedTensor** out) {
+  API_BEGIN();
+  *out = G(h)->view(member, key, which);
+  API_END();
+}
+
+int b200kv_group_size(b200kv_handle h, int* out) {
+  API_BEGIN();
+  *out = H(h)->is_group ? G(h)->size() : 1;
   API_END();
 }
 
 int b200kv_free(b200kv_handle h) {
   API_BEGIN();
-  delete S(h);
+  delete H(h);
   API_END();
 }
 
@@ -70,7 +117,7 @@ int b200kv_set_symmetric_allocator(b200kv_handle h, b200kv_symm_alloc_fn fn, voi
 
 int b200kv_wait(b200kv_handle h) {
   API_BEGIN();
-  S(h)->wait();
+  KV(h, wait());
   API_END();
 }
 
@@ -91,69 +138,73 @@ int b200kv_comm_init(b200kv_handle h, const char id[128]) {
 int b200kv_lookup_keys(b200kv_handle h, int num, const char* const* str_keys, int create,
                        int* out_keys) {
   API_BEGIN();
-  S(h)->lookup_keys(num, str_keys, create != 0, out_keys);
+  KV(h, lookup_keys(num, str_keys, create != 0, out_keys));
   API_END();
 }
 
 int b200kv_init(b200kv_handle h, int num, const int* keys, DLManagedTensor* const* vals) {
   API_BEGIN();
-  S(h)->init(num, keys, vals);
+  KV(h, init(num, keys, vals));
   API_END();
 }
 
 int b200kv_push(b200kv_handle h, int num, const int* keys, DLManagedTensor* const* vals, int) {
   API_BEGIN();
-  S(h)->dense(Store::kPush, num, keys, vals, 0, nullptr, nullptr);
+  KV(h, dense(Store::kPush, num, keys, vals, 0, nullptr, nullptr));
   API_END();
 }
 
 int b200kv_pull(b200kv_handle h, int num, const int* keys, DLManagedTensor* const* outs, int) {
   API_BEGIN();
-  S(h)->dense(Store::kPull, 0, nullptr, nullptr, num, keys, outs);
+  KV(h, dense(Store::kPull, 0, nullptr, nullptr, num, keys, outs));
   API_END();
 }
 
 int b200kv_pushpull(b200kv_handle h, int vnum, const int* vkeys, DLManagedTensor* const* vals,
                     int onum, const int* okeys, DLManagedTensor* const* outs, int) {
   API_BEGIN();
-  S(h)->dense(Store::kPushPull, vnum, vkeys, vals, onum, okeys, outs);
+  KV(h, dense(Store::kPushPull, vnum, vkeys, vals, onum, okeys, outs));
   API_END();
 }
 
 int b200kv_bind_pushpull(b200kv_handle h, int vnum, const int* vkeys, DLManagedTensor* const* vals,
                          int onum, const int* okeys, DLManagedTensor* const* outs, int* out_id) {
   API_BEGIN();
-  *out_id = S(h)->bind(Store::kPushPull, vnum, vkeys, vals, onum, okeys, outs);
+  KVR(h, *out_id, bind(Store::kPushPull, vnum, vkeys, vals, onum, okeys, outs));
   API_END();
 }
 
 int b200kv_run_bound(b200kv_handle h, int id) {
   API_BEGIN();
-  S(h)->run_bound(id);
+  KV(h, run_bound(id));
   API_END();
 }
 
 int b200kv_unbind(b200kv_handle h, int id) {
   API_BEGIN();
-  S(h)->unbind(id);
+  KV(h, unbind(id));
   API_END();
 }
 
 int b200kv_set_profiling(b200kv_handle h, int enable) {
   API_BEGIN();
-  S(h)->set_profiling(enable != 0);
+  KV(h, set_profiling(enable != 0));
   API_END();
 }
 
 int b200kv_profile_read(b200kv_handle h, double* kernel_ms, int64_t* count) {
   API_BEGIN();
-  S(h)->profile_read(kernel_ms, count);
+  double m[8];
+  int64_t c[8];
+  KV(h, profile_read_phases(m, c));
+  *kernel_ms = m[0];
+  *count = c[0];
   API_END();
 }
 
 int b200kv_profile_read_phases(b200kv_handle h, double ms[8], int64_t count[8]) {
   API_BEGIN();
-  S(h)->profile_read_phases(ms, count);
+  KV(h, profile_read_phases(ms, count));
   API_END();
 }
 
@@ -161,72 +212,72 @@ int b200kv_broadcast(b200kv_handle h, int vnum, const int* vkeys, DLManagedTenso
                      int onum, const int* okeys, DLManagedTensor* const* outs, int) {
   API_BEGIN();
   // BroadcastImpl = InitImpl; PullImpl (kvstore_local.h:327-334)
-  S(h)->init(vnum, vkeys, vals);
-  S(h)->dense(Store::kPull, 0, nullptr, nullptr, onum, okeys, outs);
+  KV(h, init(vnum, vkeys, vals));
+  KV(h, dense(Store::kPull, 0, nullptr, nullptr, onum, okeys, outs));
   API_END();
 }
 
 int b200kv_set_optimizer(b200kv_handle h, const b200kv_optimizer* opt) {
   API_BEGIN();
   KV_CHECK(opt != nullptr, "null optimizer description");
-  S(h)->set_optimizer(*opt);
+  KV(h, set_optimizer(*opt));
   API_END();
 }
 
 int b200kv_set_hyper(b200kv_handle h, int num, const int* keys, const float* lrs, const float* wds,
                      const int* steps) {
   API_BEGIN();
-  S(h)->set_hyper(num, keys, lrs, wds, steps);
+  KV(h, set_hyper(num, keys, lrs, wds, steps));
   API_END();
 }
 
 int b200kv_last_global_norm(b200kv_handle h, float* out) {
   API_BEGIN();
-  *out = S(h)->last_global_norm();
+  KVR(h, *out, last_global_norm());
   API_END();
 }
 
 int b200kv_view(b200kv_handle h, int key, int which, DLManagedTensor** out) {
   API_BEGIN();
-  *out = S(h)->view(key, which);
+  *out = H(h)->is_group ? G(h)->view(0, key, which) : S(h)->view(key, which);
   API_END();
 }
 
 int b200kv_get_state(b200kv_handle h, int key, int which, DLManagedTensor* out, int* present) {
   API_BEGIN();
-  S(h)->get_state(key, which, out, present);
+  KV(h, get_state(key, which, out, present));
   API_END();
 }
 
 int b200kv_set_state(b200kv_handle h, int key, int which, DLManagedTensor* in) {
   API_BEGIN();
-  S(h)->set_state(key, which, in);
+  KV(h, set_state(key, which, in));
   API_END();
 }
 
 int b200kv_init_rsp(b200kv_handle h, int key, DLManagedTensor* dense_value) {
   API_BEGIN();
-  S(h)->init_rsp(key, dense_value);
+  KV(h, init_rsp(key, dense_value));
   API_END();
 }
 
 int b200kv_push_rsp(b200kv_handle h, int key, int ncopies, DLManagedTensor* const* indices,
                     DLManagedTensor* const* values, int) {
   API_BEGIN();
-  S(h)->push_rsp(key, ncopies, indices, values);
+  KV(h, push_rsp(key, ncopies, indices, values));
   API_END();
 }
 
 int b200kv_rsp_merged_size(b200kv_handle h, int key, int64_t* nnr) {
   API_BEGIN();
-  *nnr = S(h)->rsp_merged_size(key);
+  KVR(h, *nnr, rsp_merged_size(key));
   API_END();
 }
 
 int b200kv_rsp_merged_copy(b200kv_handle h, int key, DLManagedTensor* out_indices,
                            DLManagedTensor* out_values) {
   API_BEGIN();
-  S(h)->rsp_merged_copy(key, out_indices, out_values);
+  KV(h, rsp_merged_copy(key, out_indices, out_values));
   API_END();
 }
 
@@ -234,43 +285,44 @@ int b200kv_row_sparse_pull(b200kv_handle h, int key, DLManagedTensor* row_ids,
                            DLManagedTensor* out_indices, DLManagedTensor* out_values,
                            int64_t* out_nnr, int) {
   API_BEGIN();
-  *out_nnr = S(h)->row_sparse_pull(key, row_ids, out_indices, out_values);
+  KVR(h, *out_nnr, row_sparse_pull(key, row_ids, out_indices, out_values));
   API_END();
 }
 
 int b200kv_get_type(b200kv_handle h, const char** out) {
   API_BEGIN();
-  *out = S(h)->type();
+  *out = "b200";
+  (void)H(h);
   API_END();
 }
 
 int b200kv_get_rank(b200kv_handle h, int* out) {
   API_BEGIN();
-  *out = S(h)->rank();
+  *out = H(h)->is_group ? 0 : S(h)->rank();
   API_END();
 }
 
 int b200kv_get_group_size(b200kv_handle h, int* out) {
   API_BEGIN();
-  *out = S(h)->world();
+  *out = H(h)->is_group ? 1 : S(h)->world();   // a group is ONE worker driving several devices
   API_END();
 }
 
 int b200kv_barrier(b200kv_handle h) {
   API_BEGIN();
-  S(h)->barrier();
+  KV(h, barrier());
   API_END();
 }
 
 int b200kv_last_exchange(b200kv_handle h, const char** out) {
   API_BEGIN();
-  *out = S(h)->last_exchange();
+  KVR(h, *out, last_exchange());
   API_END();
 }
 
 int b200kv_launch_count(b200kv_handle h, int64_t* out) {
   API_BEGIN();
-  *out = S(h)->launches();
+  KVR(h, *out, launches());
   API_END();
 }
 

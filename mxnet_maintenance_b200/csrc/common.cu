@@ -1,5 +1,6 @@
 #include "common.h"
 
+#include <algorithm>
 #include <cstring>
 #include <mutex>
 
@@ -52,6 +53,31 @@ TableRing::~TableRing() {
   }
 }
 
+static void grow_slot(void** host, void** dev, size_t* cap, size_t bytes) {
+  if (bytes <= *cap) return;
+  if (*host) cudaFreeHost(*host);
+  if (*dev) cudaFree(*dev);
+  *host = *dev = nullptr;
+  const size_t c = std::max<size_t>((bytes + 4095) & ~size_t(4095), size_t(256) << 10);
+  CUDA_OK(cudaMallocHost(host, c));
+  CUDA_OK(cudaMalloc(dev, c));
+  *cap = c;
+}
+
+void TableRing::reserve_all(size_t bytes) {
+  for (auto& s : slots_) {
+    if (bytes > s.cap) {
+      if (s.busy) {
+        CUDA_OK(cudaEventSynchronize(s.done));
+        s.busy = false;
+      }
+      if (&s == &slots_[last_ >= 0 ? last_ : 0] && last_ >= 0) last_ = -1;   // its device table goes away
+      grow_slot(&s.host, &s.dev, &s.cap, bytes);
+    }
+    if (!s.done) CUDA_OK(cudaEventCreateWithFlags(&s.done, cudaEventDisableTiming));
+  }
+}
+
 uint64_t* TableRing::begin(size_t bytes) {
   cur_ = (cur_ + 1) % kSlots;
   if (cur_ == last_) cur_ = (cur_ + 1) % kSlots;   // never stage over the table that may be reused
@@ -60,15 +86,7 @@ uint64_t* TableRing::begin(size_t bytes) {
     CUDA_OK(cudaEventSynchronize(s.done));
     s.busy = false;
   }
-  if (bytes > s.cap) {
-    if (s.host) cudaFreeHost(s.host);
-    if (s.dev) cudaFree(s.dev);
-    s.host = s.dev = nullptr;
-    const size_t cap = (bytes + 4095) & ~size_t(4095);
-    CUDA_OK(cudaMallocHost(&s.host, cap));
-    CUDA_OK(cudaMalloc(&s.dev, cap));
-    s.cap = cap;
-  }
+  grow_slot(&s.host, &s.dev, &s.cap, bytes);
   if (!s.done) CUDA_OK(cudaEventCreateWithFlags(&s.done, cudaEventDisableTiming));
   cur_bytes_ = bytes;
   return static_cast<uint64_t*>(s.host);
@@ -120,6 +138,29 @@ void ChunkPlan::build(const std::vector<int64_t>& begin, const std::vector<int64
   if (!ch.empty())
     CUDA_OK(cudaMemcpy(chunks.p, ch.data(), sizeof(Chunk) * ch.size(), cudaMemcpyHostToDevice));
   CUDA_OK(cudaMemcpy(first.p, fst.data(), sizeof(int) * fst.size(), cudaMemcpyHostToDevice));
+}
+
+static std::vector<const void*>& kernel_registry() {
+  static std::vector<const void*> v;
+  return v;
+}
+static std::mutex& kernel_registry_mu() {
+  static std::mutex m;
+  return m;
+}
+
+bool register_kernel(const void* host_stub) {
+  std::lock_guard<std::mutex> lk(kernel_registry_mu());
+  kernel_registry().push_back(host_stub);
+  return true;
+}
+
+void preload_kernels() {
+  std::lock_guard<std::mutex> lk(kernel_registry_mu());
+  for (const void* k : kernel_registry()) {
+    cudaFuncAttributes a;
+    CUDA_OK(cudaFuncGetAttributes(&a, k));
+  }
 }
 
 int sm_count(int device) {

@@ -39,6 +39,12 @@ struct Error : public std::runtime_error {
 
 void set_last_error(const std::string& msg);
 
+// What a b200kv_handle points to: a Store (one GPU per process) or a Group (one process, several GPUs)
+struct KVHandle {
+  bool is_group = false;
+  virtual ~KVHandle() = default;
+};
+
 // mshadow type flags (3rdparty/mshadow/mshadow/base.h): the dtype codes MXNet itself uses
 enum DType { kF32 = 0, kF16 = 2, kI32 = 4, kI64 = 6 };
 inline size_t dtype_size(int dt) { return dt == kF32 || dt == kI32 ? 4 : (dt == kF16 ? 2 : 8); }
@@ -100,6 +106,9 @@ class TableRing {
   void end(cudaStream_t stream);
   // the device copy of the last table was modified in place: never reuse it
   void invalidate() { last_ = -1; }
+  // make every slot hold at least `bytes` now, so that begin() never allocates later (an allocation
+  // between two launches keeps them from running concurrently — fatal when they wait for each other)
+  void reserve_all(size_t bytes);
 
  private:
   struct Slot {
@@ -132,5 +141,11 @@ struct ChunkPlan {
 };
 
 int sm_count(int device);
+
+// CUDA loads a kernel lazily at its first launch, and that load can wait for the device to drain.
+// Inside a Group a member's kernel may be spinning for a sibling whose launch would then never be
+// issued, so a Group loads every kernel of the library up front on each of its devices.
+bool register_kernel(const void* host_stub);
+void preload_kernels();   // on the current device
 
 }  // namespace b200kv

@@ -17,6 +17,10 @@ struct MtaCall {
   const P2PFlags* sync = nullptr;
   uint32_t epoch = 0;
   int sync_mode = 0;
+  // several ranks of one process share this GPU ("virtual ranks", used to exercise the multi-rank
+  // path on one device): every kernel that may wait on a peer takes 1/grid_div of the persistent
+  // grid so that all ranks' kernels are resident together
+  int grid_div = 1;
 };
 
 struct OptScalars {
@@ -68,6 +72,9 @@ int launch_sgd_staged(const MtaCall& c, bool has_mom, const OptScalars& s, const
 int launch_adam_staged(const MtaCall& c, const OptScalars& s, const float* gscale);
 int launch_copy_staged(const MtaCall& c);
 
+// deterministic all-reduce (rank order) of n <= 16384 floats through the peers' flag allocations;
+// f.epoch is the exchange's own round counter
+int launch_xsum(float* sums, int n, const P2PFlags& f, cudaStream_t stream);
 int launch_reduce_partials(const float* partials, const ChunkPlan& plan, int nred, float* sums,
                            cudaStream_t stream);
 int launch_lamb_ratio(const float* sums, int nt, float lower, float upper, float* ratio,

@@ -21,9 +21,19 @@ int grid_for(const MtaCall& c, K kernel) {
     if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, kernel, kThreads, 0) != cudaSuccess || n < 1) n = 2;
     per_sm = n;
   }
-  const int g = sm_count(c.device) * per_sm;
+  int g = sm_count(c.device) * per_sm;
+  if (c.grid_div > 1) g = std::max(1, g / c.grid_div);
   return c.plan->nchunks < g ? (c.plan->nchunks > 0 ? c.plan->nchunks : 1) : g;
 }
+
+// every instantiation that can be launched registers itself when the library is loaded
+template <class Op, typename T, typename WT, int NG>
+struct KernelReg {
+  static const bool done;
+};
+template <class Op, typename T, typename WT, int NG>
+const bool KernelReg<Op, T, WT, NG>::done =
+    register_kernel(reinterpret_cast<const void*>(&mta_kernel<Op, T, WT, NG>));
 
 MtaArgs args_of(const MtaCall& c) {
   MtaArgs a;
@@ -41,18 +51,20 @@ MtaArgs args_of(const MtaCall& c) {
 
 template <class Op, typename T, typename WT>
 int launch_ng(const MtaCall& c, const Op& op, const float* gscale, float* partials) {
-  if (c.plan->nchunks == 0) return 0;
+  // a rank whose shard of this key set is empty still takes part in the in-kernel barriers
+  if (c.plan->nchunks == 0 && (c.sync == nullptr || c.sync_mode == 0)) return 0;
   KV_CHECK(c.ngrad >= 1 && c.ngrad <= kMaxCopies, "unsupported number of gradient copies " << c.ngrad);
   KV_CHECK(c.nout >= 0 && c.nout <= kMaxCopies, "unsupported number of output copies " << c.nout);
   const MtaArgs a = args_of(c);
 #define GO(NG)                                                                                     \
+  (void)KernelReg<Op, T, WT, NG>::done;                                                            \
   mta_kernel<Op, T, WT, NG><<<grid_for(c, mta_kernel<Op, T, WT, NG>), kThreads, 0, c.stream>>>(a, op, gscale, \
                                                                                               partials)
-  if (!Op::F.read_g || c.ngrad == 1) GO(1);
-  else if (c.ngrad == 2) GO(2);
-  else if (c.ngrad == 4) GO(4);
-  else if (c.ngrad == 8) GO(8);
-  else GO(0);
+  if (!Op::F.read_g || c.ngrad == 1) { GO(1); }
+  else if (c.ngrad == 2) { GO(2); }
+  else if (c.ngrad == 4) { GO(4); }
+  else if (c.ngrad == 8) { GO(8); }
+  else { GO(0); }
 #undef GO
   CUDA_OK(cudaGetLastError());
   return 1;

@@ -759,6 +759,39 @@ static __global__ void p2p_barrier_kernel(const P2PFlags f, int which) {
   __threadfence_system();
 }
 
+// Tiny all-reduce over peer memory (replaces an ncclAllReduce of a few hundred floats between LAMB's
+// two passes / before the global-norm scale): every rank stores its n partial sums into slot `rank`
+// of every rank's exchange area, signals, waits for all, and adds the W slots IN RANK ORDER — so the
+// result is deterministic and identical on every rank.  The exchange area lives in the flag
+// allocation (byte 4096 onwards): 2 buffers (alternating with the epoch, so a fast rank's next round
+// never overwrites what a slow rank is still reading) x 8 ranks x kXsumCap floats.
+constexpr int kXsumCap = 16384;
+constexpr int kXsumFlagBase = 32;      // words [32, 40) of the flag block
+__device__ __forceinline__ float* xsum_area(uint32_t* flags) {
+  return reinterpret_cast<float*>(reinterpret_cast<char*>(flags) + 4096);
+}
+static __global__ void __launch_bounds__(256) xsum_kernel(float* __restrict__ sums, int n, const P2PFlags f) {
+  const int tid = threadIdx.x;
+  const int buf = f.epoch & 1;
+  for (int k = 0; k < f.world; ++k) {
+    float* dst = xsum_area(f.flags[k]) + static_cast<size_t>(buf * kMaxCopies + f.rank) * kXsumCap;
+    for (int i = tid; i < n; i += 256) dst[i] = sums[i];
+  }
+  __threadfence_system();
+  __syncthreads();
+  if (tid < f.world) {
+    st_release_sys(f.flags[tid] + kXsumFlagBase + f.rank, f.epoch);
+    spin_until(f.flags[f.rank] + kXsumFlagBase + tid, f.epoch, f.flags[f.rank] + 16);
+  }
+  __syncthreads();
+  const float* mine = xsum_area(f.flags[f.rank]) + static_cast<size_t>(buf) * kMaxCopies * kXsumCap;
+  for (int i = tid; i < n; i += 256) {
+    float acc = __ldcv(mine + i);
+    for (int k = 1; k < f.world; ++k) acc = __fadd_rn(acc, __ldcv(mine + static_cast<size_t>(k) * kXsumCap + i));
+    sums[i] = acc;
+  }
+}
+
 // second stage of the deterministic reduction: one warp per tensor sums that tensor's chunk
 // partials (chunks of a tensor are consecutive: [first[t], first[t+1])).  sums is [nred][nt];
 // accumulate != 0 adds to the existing value (used when a tensor list is processed in pieces).

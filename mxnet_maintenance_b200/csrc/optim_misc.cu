@@ -47,6 +47,22 @@ int launch_p2p_barrier(const P2PFlags& f, int which, cudaStream_t stream) {
   return 1;
 }
 
+static const bool g_misc_registered =
+    register_kernel(reinterpret_cast<const void*>(&xsum_kernel)) &&
+    register_kernel(reinterpret_cast<const void*>(&reduce_partials_kernel)) &&
+    register_kernel(reinterpret_cast<const void*>(&lamb_ratio_kernel)) &&
+    register_kernel(reinterpret_cast<const void*>(&global_norm_kernel)) &&
+    register_kernel(reinterpret_cast<const void*>(&p2p_barrier_kernel)) &&
+    register_kernel(reinterpret_cast<const void*>(&p2p_push_kernel));
+
+int launch_xsum(float* sums, int n, const P2PFlags& f, cudaStream_t stream) {
+  KV_CHECK(n >= 0 && n <= kXsumCap, "too many partial sums for the peer-memory exchange (" << n << " > " << kXsumCap << ")");
+  if (n == 0) return 0;
+  xsum_kernel<<<1, 256, 0, stream>>>(sums, n, f);
+  CUDA_OK(cudaGetLastError());
+  return 1;
+}
+
 int launch_reduce_partials(const float* partials, const ChunkPlan& plan, int nred, float* sums,
                            cudaStream_t stream) {
   if (plan.nt == 0) return 0;

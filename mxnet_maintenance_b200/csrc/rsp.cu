@@ -101,11 +101,16 @@ void unique_heads(RspKey& k, const uint32_t* keys, int n, cudaStream_t st, int64
 
 }  // namespace
 
+// inside a Group the arrays of a call may live on any device of the process (peer memory)
+static int dev_of(const DLManagedTensor* t, bool in_process, int own) {
+  return (in_process && t != nullptr) ? t->dl_tensor.device.device_id : own;
+}
+
 void Store::init_rsp(int key, DLManagedTensor* dense_value) {
   use_device();
   if (key_type_ < 0) key_type_ = 0;
   KV_CHECK(keys_.find(key) == keys_.end() && rsp_.find(key) == rsp_.end(), "duplicate init of key " << key);
-  const TensorView v = view_of(dense_value, device_, "row-sparse init value");
+  const TensorView v = view_of(dense_value, dev_of(dense_value, in_process_, device_), "row-sparse init value");
   KV_CHECK(v.dtype == kF32, "row-sparse keys are float32");
   KV_CHECK(v.ndim >= 2, "row-sparse init needs a [num_rows, ...] table");
   std::shared_ptr<RspKey> k(new RspKey());
@@ -115,9 +120,8 @@ void Store::init_rsp(int key, DLManagedTensor* dense_value) {
   KV_CHECK(k->num_rows < (int64_t(1) << 32), "row-sparse tables are limited to 2^32 rows");
   k->bits = bits_for(k->num_rows);
   k->table.reserve(static_cast<size_t>(v.numel) * 4 + 16);
-  CUDA_OK(cudaMemcpyAsync(k->table.p, v.data, static_cast<size_t>(v.numel) * 4, cudaMemcpyDeviceToDevice,
-                          stream_));
-  if (world_ > 1) {
+  CUDA_OK(cudaMemcpyAsync(k->table.p, v.data, static_cast<size_t>(v.numel) * 4, cudaMemcpyDefault, stream_));
+  if (world_ > 1 && !in_process_) {
     KV_CHECK(comm_, "b200kv_comm_init has not been called");
     NCCL_OK(NcclApi::get().Broadcast(k->table.p, k->table.p, v.numel, ncclFloat32, 0,
                                      reinterpret_cast<ncclComm_t>(comm_), stream_));
@@ -143,8 +147,8 @@ void Store::push_rsp(int key, int ncopies, DLManagedTensor* const* idx, DLManage
   int64_t total = 0;
   int n = 0;
   for (int c = 0; c < ncopies; ++c) {
-    const TensorView vi = view_of(idx[c], device_, "row-sparse indices");
-    const TensorView vv = view_of(val[c], device_, "row-sparse values");
+    const TensorView vi = view_of(idx[c], dev_of(idx[c], in_process_, device_), "row-sparse indices");
+    const TensorView vv = view_of(val[c], dev_of(val[c], in_process_, device_), "row-sparse values");
     KV_CHECK(vi.dtype == kI64, "row-sparse indices must be int64 (src/ndarray/ndarray.cc:65)");
     KV_CHECK(vv.dtype == kF32, "row-sparse values must be float32");
     KV_CHECK(vv.numel == vi.numel * k.row_len, "values must be [nnr, " << k.row_len << "]");
@@ -157,7 +161,7 @@ void Store::push_rsp(int key, int ncopies, DLManagedTensor* const* idx, DLManage
   }
   in.n = n;
   in.start[n] = total;
-  if (world_ > 1) {
+  if (world_ > 1 && !in_process_) {
     // Every rank holds the whole table (replicated), so the exchange is an all-gather of the
     // ranks' (ids, rows); afterwards each rank reduces and updates identically.  Rank r's rows keep
     // their device order and ranks are concatenated in rank order = the reference's device order.
@@ -318,7 +322,7 @@ int64_t Store::row_sparse_pull(int key, DLManagedTensor* row_ids, DLManagedTenso
   auto it = rsp_.find(key);
   KV_CHECK(it != rsp_.end(), "key " << key << " has not been initialized as row_sparse");
   RspKey& k = *it->second;
-  const TensorView ids = view_of(row_ids, device_, "row_ids");
+  const TensorView ids = view_of(row_ids, dev_of(row_ids, in_process_, device_), "row_ids");
   const TensorView vi = view_of(out_idx, device_, "row_sparse_pull indices out");
   const TensorView vv = view_of(out_val, device_, "row_sparse_pull values out");
   KV_CHECK(ids.dtype == kI64 || ids.dtype == kI32 || ids.dtype == kF32, "row_ids must be int64, int32 or float32");

@@ -19,6 +19,7 @@ int launch_cast(const void* src, int src_dtype, void* dst, int dst_dtype, int64_
 namespace {
 
 int64_t align_up(int64_t x, int64_t a) { return (x + a - 1) / a * a; }
+constexpr int kXsumCapHost = 16384;   // optim.cuh kXsumCap
 
 struct Blob {
   uint64_t* p;
@@ -45,7 +46,8 @@ inline char* at(const DevBuf& b, int64_t elem, size_t esize) {
 
 }  // namespace
 
-Store::Store(int device, int rank, int world) : device_(device), rank_(rank), world_(world) {
+Store::Store(int device, int rank, int world, bool in_process, int grid_share)
+    : device_(device), rank_(rank), world_(world), in_process_(in_process), grid_share_(grid_share) {
   KV_CHECK(world >= 1 && rank >= 0 && rank < world, "invalid rank " << rank << " / world " << world);
   int n = 0;
   CUDA_OK(cudaGetDeviceCount(&n));
@@ -62,7 +64,7 @@ Store::~Store() {
   cudaStreamSynchronize(stream_);
   for (auto& sp : segs_) {   // unmap the peers' buffers before our own are freed
     Segment::P2P& P = sp->p2p;
-    if (!P.ok || P.symmetric) continue;   // symmetric mappings belong to the host-side allocator
+    if (!P.ok || P.symmetric || in_process_) continue;   // symmetric / sibling memory is not ours to unmap
     for (int k = 0; k < world_; ++k) {
       if (k == rank_) continue;
       if (P.g[k]) cudaIpcCloseMemHandle(P.g[k]);
@@ -107,7 +109,7 @@ void Store::comm_init(const char id[128]) {
 
 void Store::barrier() {
   use_device();
-  if (world_ > 1) {
+  if (world_ > 1 && !in_process_) {
     KV_CHECK(comm_, "b200kv_comm_init has not been called");
     DevBuf tmp;
     tmp.reserve(16);
@@ -164,7 +166,7 @@ void Store::init(int num, const int* keys, DLManagedTensor* const* vals) {
     k.staged->reserve(bytes ? bytes : 16);
     if (bytes)
       CUDA_OK(cudaMemcpyAsync(k.staged->p, v.data, bytes, cudaMemcpyDeviceToDevice, stream_));
-    if (world_ > 1 && bytes) {  // every rank starts from rank 0's value
+    if (world_ > 1 && bytes && !in_process_) {  // every rank starts from rank 0's value
       KV_CHECK(comm_, "b200kv_comm_init has not been called");
       NCCL_OK(NcclApi::get().Broadcast(k.staged->p, k.staged->p, v.numel, nccl_type(v.dtype), 0,
                                        reinterpret_cast<ncclComm_t>(comm_), stream_));
@@ -356,9 +358,7 @@ const float* Store::global_norm_scale(DensePlan& p, const ChunkPlan& cp, const M
   float* sums = p.sums.as<float>();
   launches_ += launch_sumsq(c, partials);
   launches_ += launch_reduce_partials(partials, cp, 1, sums, stream_);
-  if (world_ > 1)
-    NCCL_OK(NcclApi::get().AllReduce(sums, sums, c.nt, ncclFloat32, ncclSum,
-                                     reinterpret_cast<ncclComm_t>(comm_), stream_));
+  if (world_ > 1) allreduce_sums(*segs_[p.seg], sums, c.nt);
   launches_ += launch_global_norm(sums, c.nt, opt_.clip_global_norm, gnorm_.as<float>(), stream_);
   gnorm_valid_ = true;
   return gnorm_.as<float>();
@@ -388,8 +388,7 @@ void Store::update_chunks(DensePlan& p, const ChunkPlan& cp, const MtaCall& call
       launches_ += launch_lamb1(c1, sc_, gscale, partials, keep_u);
       launches_ += launch_reduce_partials(partials, cp, 2, sums, stream_);
       if (world_ > 1)  // per-tensor norms span shards: one tiny all-reduce between the two passes
-        NCCL_OK(NcclApi::get().AllReduce(sums, sums, 2 * static_cast<size_t>(c.nt), ncclFloat32, ncclSum,
-                                         reinterpret_cast<ncclComm_t>(comm_), stream_));
+        allreduce_sums(*segs_[p.seg], sums, 2 * c.nt);
       launches_ += launch_lamb_ratio(sums, c.nt, sc_.lower, sc_.upper, ratio, stream_);
       launches_ += keep_u ? launch_lamb2u(c2, ratio) : launch_lamb2(c2, sc_, ratio);
       break;
@@ -397,6 +396,20 @@ void Store::update_chunks(DensePlan& p, const ChunkPlan& cp, const MtaCall& call
     default:
       KV_CHECK(false, "no optimizer set");
   }
+}
+
+void Store::allreduce_sums(Segment& s, float* sums, int n) {
+  static const bool use_nccl = [] { const char* e = getenv("B200KV_XSUM"); return e && e[0] == '0'; }();
+  if (s.p2p.ok && (in_process_ || !use_nccl) && n <= kXsumCapHost) {
+    P2PFlags f;
+    for (int k = 0; k < kMaxCopies; ++k) f.flags[k] = s.p2p.flags[k];
+    f.world = world_; f.rank = rank_; f.epoch = ++s.p2p.xepoch;
+    launches_ += launch_xsum(sums, n, f, stream_);
+    return;
+  }
+  KV_CHECK(comm_ != nullptr, "no communicator for the partial-sum all-reduce");
+  NCCL_OK(NcclApi::get().AllReduce(sums, sums, static_cast<size_t>(n), ncclFloat32, ncclSum,
+                                   reinterpret_cast<ncclComm_t>(comm_), stream_));
 }
 
 float Store::last_global_norm() {
@@ -420,9 +433,9 @@ void Store::run_class(Mode mode, DensePlan& p, const std::vector<const Entry*>& 
              "float16 weights need multi_precision=True (pure fp16 optimizer state is not supported)");
     ensure_states(s);
   }
-  NcclApi* nccl = world_ > 1 ? &NcclApi::get() : nullptr;
+  NcclApi* nccl = world_ > 1 && !in_process_ ? &NcclApi::get() : nullptr;
   ncclComm_t comm = reinterpret_cast<ncclComm_t>(comm_);
-  if (world_ > 1) KV_CHECK(comm_, "b200kv_comm_init has not been called");
+  if (world_ > 1 && !in_process_) KV_CHECK(comm_, "b200kv_comm_init has not been called");
 
   // carve all tables of this call out of one ring slot
   const int ng = push ? p.ngrad : 1, no = pull ? p.nout : 0;
@@ -440,6 +453,7 @@ void Store::run_class(Mode mode, DensePlan& p, const std::vector<const Entry*>& 
   base.dtype = s.dtype;
   base.stream = stream_;
   base.device = device_;
+  base.grid_div = grid_share_;
 
   auto fill_update_scalars = [&](Blob& b) {
     for (int t = 0; t < nt; ++t) {
@@ -530,6 +544,14 @@ void Store::run_class(Mode mode, DensePlan& p, const std::vector<const Entry*>& 
   // ---------------- world > 1: pack -> reduce-scatter -> sharded update -> all-gather -> unpack
   if (push) last_exchange_ = "nccl";
   if (s.gbuf.p == nullptr && push) alloc_gbuf(s);
+  if (push && in_process_) {
+    // one process, several GPUs: every push — whole model or one key, with or without an optimizer —
+    // runs as the fused peer-memory kernel (the Group linked the members' buffers beforehand)
+    KV_CHECK(s.p2p.ok, "internal: segment not linked to its peers");
+    ring_.end(stream_);
+    run_class_p2p(p, s, ents, pull, g_alias, o_alias);
+    return;
+  }
   if (push && has_opt() && p.full_segment) {
     if (!s.p2p.tried) setup_p2p(s);
     if (s.p2p.ok) {
@@ -768,13 +790,13 @@ void Store::run_class_p2p(DensePlan& p, Segment& s, const std::vector<const Entr
                           bool g_alias, bool o_alias) {
   const int nt = static_cast<int>(p.keys.size());
   const size_t es = dtype_size(s.dtype);
-  const bool mp = use_mp(s);
+  const bool mp = has_opt() && use_mp(s);
   const int W = world_;
   Segment::P2P& P = s.p2p;
   const int ng = p.ngrad, no = pull ? p.nout : 0;
   // LAMB and global-norm clipping make several passes over the merged gradient: reduce the shard
   // into the local bucket once instead of crossing NVLink on every pass
-  const bool prereduce = opt_.kind == B200KV_OPT_LAMB || opt_.clip_global_norm >= 0.f;
+  const bool prereduce = has_opt() && (opt_.kind == B200KV_OPT_LAMB || opt_.clip_global_norm >= 0.f);
   static const bool staged_env = [] { const char* e = getenv("B200KV_STAGED"); return e && e[0] == '1'; }();
   static const bool push_env = [] { const char* e = getenv("B200KV_PUSH"); return e && e[0] == '1'; }();
   const bool staged = staged_env;
@@ -839,7 +861,8 @@ void Store::run_class_p2p(DensePlan& p, Segment& s, const std::vector<const Entr
           u.O(o++, t, static_cast<char*>(P.w[k]) + ki.off * es);
         }
       }
-      u.S(kSecW, t, mp ? at(s.master, ki.off - s.state_begin, 4) : at(s.wbuf, ki.off, 4));
+      u.S(kSecW, t, mp ? at(s.master, ki.off - s.state_begin, 4) : at(s.wbuf, ki.off, es));
+      if (!has_opt()) continue;   // no updater: the merged value is assigned (kvstore_local.h:268-274)
       if (s.has_s0) u.S(kSecS0, t, at(s.s0, ki.off - s.state_begin, 4));
       if (s.has_s1) u.S(kSecS1, t, at(s.s1, ki.off - s.state_begin, 4));
       if (s.xbuf.p) u.S(kSecX, t, at(s.xbuf, ki.off - s.state_begin, 4));
@@ -860,6 +883,7 @@ void Store::run_class_p2p(DensePlan& p, Segment& s, const std::vector<const Entr
   const uint64_t* dev = ring_.commit(stream_);
   MtaCall base;
   base.nt = nt; base.dtype = s.dtype; base.stream = stream_; base.device = device_;
+  base.grid_div = grid_share_;
 
   MtaCall c = base;
   c.blob = dev + o_pack; c.ngrad = ng; c.nout = 0; c.plan = &p.full;
@@ -902,8 +926,13 @@ void Store::run_class_p2p(DensePlan& p, Segment& s, const std::vector<const Entr
   if (fold) { u.sync = dsync; u.epoch = f.epoch; u.sync_mode = (prereduce ? 0 : kSyncWaitReady) | kSyncSignalDone; }
   if (nvls) u.sync_mode |= kSyncMcOut | (prereduce ? 0 : kSyncMcGrad);
   prof_begin(0);
-  const float* gscale = opt_.clip_global_norm >= 0.f ? global_norm_scale(p, p.shard, u) : nullptr;
-  update_chunks(p, p.shard, u, gscale);
+  if (has_opt()) {
+    const float* gscale = opt_.clip_global_norm >= 0.f ? global_norm_scale(p, p.shard, u) : nullptr;
+    update_chunks(p, p.shard, u, gscale);
+  } else {
+    u.plan = &p.shard;
+    launches_ += launch_copy(u, true, true);   // merged shard -> the stored value on every rank
+  }
   prof_end();
 
   if (!fold) {
@@ -1000,6 +1029,20 @@ void Store::prepare(Mode mode, int vnum, const int* vkeys, DLManagedTensor* cons
     ks.reserve(c.ents.size());
     for (const Entry* e : c.ents) ks.push_back(e->key);
     c.plan = &plan_for(c.seg, ks, c.ng, c.no);
+  }
+}
+
+void Store::preallocate(BoundCall& bc) {
+  size_t table_bytes = 0;
+  for (auto& c : bc.classes)   // upper bound of the tables run_class / run_class_p2p carve out of a ring slot
+    table_bytes = std::max(table_bytes, 8 * 4 * mta_blob_words(static_cast<int>(c.plan->keys.size()),
+                                                                std::max(c.ng, world_), std::max(c.no, world_)));
+  ring_.reserve_all(table_bytes);
+  for (auto& c : bc.classes) {
+    if (!(c.mode & kPush) || !has_opt()) continue;
+    Segment& s = *segs_[c.plan->seg];
+    if (s.dtype == kF16 && !opt_.multi_precision) continue;   // rejected with a message in run_class
+    ensure_states(s);
   }
 }
 
@@ -1178,6 +1221,109 @@ void Store::set_state(int key, int which, DLManagedTensor* in) {
       }
       NCCL_OK(nccl.GroupEnd());
     }
+  }
+}
+
+// ---- members of a Group (one process driving several GPUs) ------------------------------------------
+void Store::init_any_device(int key, DLManagedTensor* val) {
+  use_device();
+  if (key_type_ < 0) key_type_ = 0;
+  KV_CHECK(keys_.find(key) == keys_.end() && rsp_.find(key) == rsp_.end(), "duplicate init of key " << key);
+  KV_CHECK(val != nullptr, "init value: null DLManagedTensor");
+  const int src_dev = val->dl_tensor.device.device_id;
+  const TensorView v = view_of(val, src_dev, "init value");
+  KV_CHECK(v.dtype == kF32 || v.dtype == kF16, "init: only float32/float16 values are supported");
+  KeyInfo k;
+  k.key = key;
+  k.dtype = v.dtype;
+  k.size = v.numel;
+  k.staged.reset(new DevBuf());
+  const size_t bytes = static_cast<size_t>(v.numel) * dtype_size(v.dtype);
+  k.staged->reserve(bytes ? bytes : 16);
+  if (bytes) {
+    if (src_dev == device_)
+      CUDA_OK(cudaMemcpyAsync(k.staged->p, v.data, bytes, cudaMemcpyDeviceToDevice, stream_));
+    else
+      CUDA_OK(cudaMemcpyPeerAsync(k.staged->p, device_, v.data, src_dev, bytes, stream_));
+  }
+  keys_.emplace(key, std::move(k));
+  unsealed_.push_back(key);
+}
+
+void Store::link_peers(int seg, const std::vector<Store*>& all) {
+  use_device();
+  Segment& s = *segs_[seg];
+  Segment::P2P& P = s.p2p;
+  if (P.ok) return;
+  P.tried = true;
+  for (int k = 0; k < world_; ++k) {
+    Segment& o = *all[k]->segs_[seg];
+    KV_CHECK(o.total == s.total && o.dtype == s.dtype, "internal: members disagree on the segment layout");
+    P.g[k] = o.gbuf.p;
+    P.w[k] = o.wbuf.p;
+    P.flags[k] = o.p2p.local_flags.as<uint32_t>();
+    P.stage[k] = nullptr;
+  }
+  P2PFlags h;
+  std::memset(&h, 0, sizeof(h));
+  for (int k = 0; k < world_; ++k) h.flags[k] = P.flags[k];
+  h.world = world_;
+  h.rank = rank_;
+  P.dev_sync.reserve(sizeof(P2PFlags));
+  CUDA_OK(cudaMemcpy(P.dev_sync.p, &h, sizeof(h), cudaMemcpyHostToDevice));
+  P.ok = true;
+}
+
+bool Store::copy_state_shard(int key, int which, float* dst, int dst_device, int64_t numel) {
+  use_device();
+  const KeyInfo& ki = info(key);
+  KV_CHECK(which >= 0 && which <= 2, "state selector must be 0, 1 or 2");
+  KV_CHECK(numel == ki.size, "state out must hold " << ki.size << " elements");
+  if (ki.seg < 0) return false;
+  Segment& s = *segs_[ki.seg];
+  const DevBuf* src = which == 0 ? (s.has_s0 ? &s.s0 : nullptr)
+                    : which == 1 ? (s.has_s1 ? &s.s1 : nullptr) : (s.has_master ? &s.master : nullptr);
+  if (!src) return false;
+  const int64_t lo = std::max(ki.off, s.state_begin), hi = std::min(ki.off + ki.size, s.state_begin + s.state_len);
+  if (lo < hi)
+    CUDA_OK(cudaMemcpyPeerAsync(dst + (lo - ki.off), dst_device, at(*src, lo - s.state_begin, 4), device_,
+                                static_cast<size_t>(hi - lo) * 4, stream_));
+  return true;
+}
+
+void Store::load_state_shard(int key, int which, const float* src, int src_device, int64_t numel) {
+  use_device();
+  const KeyInfo& ki0 = info(key);
+  KV_CHECK(which >= 0 && which <= 2, "state selector must be 0, 1 or 2");
+  KV_CHECK(has_opt(), "set_state needs an optimizer");
+  KV_CHECK(numel == ki0.size, "state must hold " << ki0.size << " elements");
+  if (ki0.seg < 0) seal();
+  const KeyInfo& ki = keys_[key];
+  Segment& s = *segs_[ki.seg];
+  ensure_states(s);
+  DevBuf* dst = which == 0 ? (s.has_s0 ? &s.s0 : nullptr)
+              : which == 1 ? (s.has_s1 ? &s.s1 : nullptr) : (s.has_master ? &s.master : nullptr);
+  KV_CHECK(dst, "the current optimizer keeps no such state");
+  const int64_t lo = std::max(ki.off, s.state_begin), hi = std::min(ki.off + ki.size, s.state_begin + s.state_len);
+  if (lo < hi) {
+    CUDA_OK(cudaMemcpyPeerAsync(at(*dst, lo - s.state_begin, 4), device_, src + (lo - ki.off), src_device,
+                                static_cast<size_t>(hi - lo) * 4, stream_));
+    if (which == 2)   // the fp16 stored value follows its master
+      launches_ += launch_cast(at(*dst, lo - s.state_begin, 4), kF32, at(s.wbuf, lo, 2), kF16, hi - lo, stream_);
+  }
+}
+
+void Store::spread_fp16_shard(int key, const std::vector<Store*>& all) {
+  use_device();
+  const KeyInfo& ki = info(key);
+  Segment& s = *segs_[ki.seg];
+  const int64_t lo = std::max(ki.off, s.state_begin), hi = std::min(ki.off + ki.size, s.state_begin + s.state_len);
+  if (lo >= hi) return;
+  for (Store* o : all) {
+    if (o == this) continue;
+    Segment& os = *o->segs_[ki.seg];
+    CUDA_OK(cudaMemcpyPeerAsync(at(os.wbuf, lo, 2), o->device_, at(s.wbuf, lo, 2), device_,
+                                static_cast<size_t>(hi - lo) * 2, stream_));
   }
 }
 

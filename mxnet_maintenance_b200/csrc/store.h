@@ -57,6 +57,7 @@ struct Segment {
     DevBuf local_flags;
     DevBuf dev_sync;     // P2PFlags resident on the device for the in-kernel barriers
     uint32_t epoch = 0;
+    uint32_t xepoch = 0;   // round counter of the partial-sum exchange (xsum_kernel)
   } p2p;
 };
 
@@ -73,10 +74,15 @@ struct DensePlan {
 
 struct RspKey;  // rsp.cu
 
-class Store {
+class Group;
+
+class Store : public KVHandle {
  public:
-  Store(int device, int rank, int world);
-  ~Store();
+  // in_process: this store is one member of a Group (group.cu) — W ranks inside ONE process, the
+  // reference's own usage model.  No NCCL communicator exists then: every exchange goes through
+  // peer memory.  grid_share: number of members driving this same physical GPU.
+  Store(int device, int rank, int world, bool in_process = false, int grid_share = 1);
+  ~Store() override;
 
   void set_stream(cudaStream_t s) { stream_ = s; }
   void set_symmetric_allocator(b200kv_symm_alloc_fn fn, void* ctx) { symm_alloc_ = fn; symm_ctx_ = ctx; }
@@ -116,6 +122,23 @@ class Store {
   int64_t row_sparse_pull(int key, DLManagedTensor* row_ids, DLManagedTensor* out_idx,
                           DLManagedTensor* out_val);
 
+  // ---- used by Group (single process, several GPUs) -------------------------------------------------
+  friend class Group;
+  int device() const { return device_; }
+  cudaStream_t stream() const { return stream_; }
+  // value may live on any GPU of the process (peer copy)
+  void init_any_device(int key, DLManagedTensor* val);
+  // wire this member's segment `seg` to its siblings' buffers (all members hold the same layout)
+  void link_peers(int seg, const std::vector<Store*>& all);
+  int num_segments() const { return static_cast<int>(segs_.size()); }
+  bool segment_linked(int seg) const { return segs_[seg]->p2p.ok; }
+  // copy this member's shard of a state array of `key` into dst (full-key fp32 array on dst_device)
+  bool copy_state_shard(int key, int which, float* dst, int dst_device, int64_t numel);
+  void load_state_shard(int key, int which, const float* src, int src_device, int64_t numel);
+  // after load_state_shard(which = 2) on every member: refresh every member's fp16 value from the owners
+  void spread_fp16_shard(int key, const std::vector<Store*>& all);
+  int64_t key_size(int key) { return info(key).size; }
+
   int rank() const { return rank_; }
   int world() const { return world_; }
   int64_t launches() const { return launches_; }
@@ -140,6 +163,9 @@ class Store {
   void prepare(Mode mode, int vnum, const int* vkeys, DLManagedTensor* const* vals, int onum,
                const int* okeys, DLManagedTensor* const* outs, BoundCall* bc, bool allow_staged);
   void execute(BoundCall& bc);
+  // allocate whatever the call's classes will need (optimizer state): a Group does this for every
+  // member before any member launches a kernel that waits for its siblings
+  void preallocate(BoundCall& bc);
   void prof_begin(int phase = 0);
   void prof_end();
   KeyInfo& info(int key);
@@ -163,7 +189,13 @@ class Store {
   bool has_opt() const { return opt_.kind != B200KV_OPT_NONE; }
   bool use_mp(const Segment& s) const { return s.dtype == kF16 && opt_.multi_precision != 0; }
 
+  // all-reduce of a few partial sums between kernels: peer-memory exchange when the segment's flag
+  // blocks are mapped (always inside a Group), ncclAllReduce otherwise
+  void allreduce_sums(Segment& s, float* sums, int n);
+
   int device_, rank_, world_;
+  bool in_process_ = false;
+  int grid_share_ = 1;
   cudaStream_t stream_ = nullptr;
   ncclComm* comm_ = nullptr;
   int key_type_ = -1;  // -1 unknown, 0 int, 1 str

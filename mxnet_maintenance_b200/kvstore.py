@@ -73,6 +73,34 @@ def _numel(x):
     return int(x.numel()) if hasattr(x, "numel") else int(x.size)
 
 
+def _dev_index(x):
+    """CUDA ordinal an array lives on (torch tensor or NDArray), or None."""
+    if _is_rsp(x):
+        x = x.data
+    if x is None:
+        return None
+    if torch is not None and isinstance(x, torch.Tensor):
+        return x.device.index if x.is_cuda else None
+    ctx = getattr(x, "context", None)
+    return getattr(ctx, "device_id", None)
+
+
+def _arrays_of(x):
+    """Every array inside a (nested) list argument."""
+    if x is None:
+        return []
+    if _is_array(x):
+        return [x]
+    out = []
+    for y in x:
+        out += _arrays_of(y)
+    return out
+
+
+def _clone(x):
+    return x.clone() if hasattr(x, "clone") else x.copy()
+
+
 def _flatten(keys, vals):
     """_ctype_key_value (python/mxnet/kvstore/base.py:32-64): a list under a scalar key means
     'device copies of that key'.  Returns (keys, arrays, use_str_keys)."""
@@ -181,20 +209,45 @@ class B200(KVStoreBase):
         is what makes a step a handful of launches.
     """
 
-    def __init__(self, device_id=None, rank=None, world_size=None):
+    def __init__(self, device_id=None, rank=None, world_size=None, devices=None):
+        """Three ways to come up:
+          * under an initialised torch.distributed group (torchrun): one store per process / GPU,
+            exchanging with its peers over NVLink (b200kv_create + communicator);
+          * ``devices=[0, 1, ...]``: ONE process driving these GPUs (b200kv_create_group) — what
+            ``mx.kv.create('device')`` is in the reference; a device may be listed several times
+            (virtual ranks on one GPU, used by the single-GPU tests);
+          * neither (``mx.kv.create('b200')`` passes no arguments): the device set is taken from the
+            arrays of the first calls — ``init`` values are held back until a call names the
+            per-device arrays (Trainer's ``broadcast(idx, w0, all_w)``, a ``push`` / ``pull`` with a
+            list) — and a group is made when they span several GPUs.
+        """
         self._lib = _lib.load()
         dist = torch is not None and torch.distributed.is_available() and torch.distributed.is_initialized()
         if rank is None:
             rank = torch.distributed.get_rank() if dist else 0
         if world_size is None:
             world_size = torch.distributed.get_world_size() if dist else 1
-        if device_id is None:
-            device_id = int(os.environ.get("LOCAL_RANK", "0")) if world_size > 1 else (
-                torch.cuda.current_device() if torch is not None and torch.cuda.is_available() else 0)
-        self._device, self._rank, self._world = device_id, rank, world_size
-        h = C.c_void_p()
-        check_call(self._lib.b200kv_create(device_id, rank, world_size, C.byref(h)))
-        self._h = h
+        self._rank, self._world = rank, world_size
+        self._handle = None
+        self._members = None            # device ordinal of every member of a group
+        self._seen = []                 # devices named by the arrays seen so far (lazy creation)
+        self._deferred = []             # (keys, cloned values) of init calls made before the handle exists
+        self._deferred_keys = set()
+        self._lazy = False
+        if devices is not None:
+            assert world_size == 1, "devices=[...] is the single-process mode"
+            self._device = int(devices[0])
+            self._create(list(devices))
+        elif world_size > 1 or device_id is not None:
+            if device_id is None:
+                device_id = int(os.environ.get("LOCAL_RANK", "0"))
+            self._device = device_id
+            h = C.c_void_p()
+            check_call(self._lib.b200kv_create(device_id, rank, world_size, C.byref(h)))
+            self._handle = h
+        else:
+            self._lazy = True
+            self._device = torch.cuda.current_device() if torch is not None and torch.cuda.is_available() else 0
         self._cache = HandleCache()
         self._updater = None
         self._opt_sent = None
@@ -213,24 +266,70 @@ class B200(KVStoreBase):
         self.auto_batch = os.environ.get("B200KV_AUTO_BATCH", "0") == "1"
         self._pending = []
         self._auto_steps = {}
-        self._bind_stream()
+        if self._handle is not None:
+            self._bind_stream()
         if world_size > 1:
             self._init_comm()
 
     # ------------------------------------------------------------------ plumbing
     def __del__(self):
-        h, self._h = getattr(self, "_h", None), None
+        h, self._handle = getattr(self, "_handle", None), None
         if h:
             try:
                 self._lib.b200kv_free(h)
             except Exception:
                 pass
 
+    def _create(self, devices):
+        """One store for one device, a group for several (or for a device listed more than once)."""
+        h = C.c_void_p()
+        if len(devices) == 1:
+            check_call(self._lib.b200kv_create(devices[0], 0, 1, C.byref(h)))
+            self._members = None
+        else:
+            check_call(self._lib.b200kv_create_group(len(devices), (C.c_int * len(devices))(*devices), C.byref(h)))
+            self._members = list(devices)
+        self._device = devices[0]
+        self._handle = h
+
+    def _note(self, arrays):
+        """Lazy mode: remember which GPUs the caller's arrays live on (until the handle exists)."""
+        if self._handle is None:
+            for a in arrays:
+                d = _dev_index(a)
+                if d is not None and d not in self._seen:
+                    self._seen.append(d)
+
+    @property
+    def _h(self):
+        if self._handle is None:
+            self._create(self._seen or [self._device])
+            self._bind_stream()
+            if self._opt_sent is not None:     # set_optimizer came first (trainer.py:254-256)
+                self._opt_sent = None
+                self._send_optimizer()
+            deferred, self._deferred = self._deferred, []
+            for key, value in deferred:
+                self.init(key, value)
+        return self._handle
+
+    @property
+    def devices(self):
+        """GPUs this store drives (one entry per member of a group)."""
+        self._h
+        return list(self._members) if self._members else [self._device]
+
     def _bind_stream(self):
         """Run on the host framework's current stream so ordering with its kernels is implicit."""
-        if torch is not None and torch.cuda.is_available():
+        if torch is None or not torch.cuda.is_available() or self._handle is None:
+            return
+        if self._members:
+            n = len(self._members)
+            ss = (C.c_void_p * n)(*[torch.cuda.current_stream(d).cuda_stream for d in self._members])
+            check_call(self._lib.b200kv_group_set_streams(self._handle, n, ss))
+        else:
             s = torch.cuda.current_stream(self._device).cuda_stream
-            check_call(self._lib.b200kv_set_stream(self._h, C.c_void_p(s)))
+            check_call(self._lib.b200kv_set_stream(self._handle, C.c_void_p(s)))
 
     def _init_comm(self):
         """KVStoreNCCL::InitNCCL (kvstore_nccl.h:475-493), one process per GPU: rank 0 creates the
@@ -330,6 +429,9 @@ class B200(KVStoreBase):
                         o.lower_bound if o.lower_bound else -1.0,
                         o.upper_bound if o.upper_bound else -1.0, gclip)
         if desc != self._opt_sent:
+            if self._handle is None:        # lazy mode: sent when the handle comes up
+                self._opt_sent = desc
+                return
             d = OptimizerDesc(*desc)
             check_call(self._lib.b200kv_set_optimizer(self._h, C.byref(d)))
             self._opt_sent = desc
@@ -351,6 +453,20 @@ class B200(KVStoreBase):
     def init(self, key, value):
         """kvstore.py:120-176.  Row-sparse values initialise a row-sparse key."""
         keys, vals, use_str = _flatten(key, value)
+        if self._handle is None and self._lazy:
+            # which GPUs take part is not known yet (KVStoreLocal::InitImpl gets ONE value per key,
+            # kvstore_local.h:226-237): keep a private copy, like the store's own copy on init
+            self._note(vals)
+            if self._str_keys is None:
+                self._str_keys = use_str
+            if self._str_keys != use_str:
+                raise B200KVError("inconsistent key types: mixing int and string keys is not allowed")
+            for k in keys:
+                if k in self._deferred_keys:
+                    raise B200KVError("duplicate init of key %s" % str(k))
+                self._deferred_keys.add(k)
+            self._deferred.append((keys, [v if _is_rsp(v) else _clone(v) for v in vals]))
+            return
         ck = self._keys(keys, use_str, create=True)
         self._bind_stream()
         dense_idx = [i for i, v in enumerate(vals) if not _is_rsp(v)]
@@ -370,6 +486,7 @@ class B200(KVStoreBase):
         """kvstore.py:178-270."""
         self.flush()
         keys, vals, use_str = _flatten(key, value)
+        self._note(vals)
         if vals and _is_rsp(vals[0]):
             return self._push_rsp(keys, vals, use_str, priority)
         ck = self._keys(keys, use_str)
@@ -383,6 +500,7 @@ class B200(KVStoreBase):
         assert out is not None
         self.flush()
         keys, outs, use_str = _flatten(key, out)
+        self._note(outs)
         if ignore_sparse:
             sel = [i for i, o in enumerate(outs) if not _is_rsp(o)]
             keys, outs = [keys[i] for i in sel], [outs[i] for i in sel]
@@ -426,6 +544,10 @@ class B200(KVStoreBase):
 
     def pushpull(self, key, value, out=None, priority=0):
         """kvstore.py:338-415: push then pull; with out=None the result lands in `value`."""
+        if self._handle is None:
+            self._note(_arrays_of(value))
+            self._note(_arrays_of(out))
+            self._h
         if self.auto_batch and isinstance(key, (int, str)) and key in self._sizes \
                 and not _is_rsp(value if _is_array(value) else value[0]):
             if any(k == key for k, _, _ in self._pending):
@@ -441,6 +563,8 @@ class B200(KVStoreBase):
         else:
             okeys, outs, use_str_o = _flatten(key, out)
             assert use_str == use_str_o
+        self._note(vals)
+        self._note(outs)
         cv = self._keys(vkeys, use_str)
         co = cv if okeys is vkeys else self._keys(okeys, use_str)
         self._bind_stream()
@@ -459,6 +583,8 @@ class B200(KVStoreBase):
             okeys, outs = vkeys, vals
         else:
             okeys, outs, _ = _flatten(key, out)
+        self._note(vals)
+        self._note(outs)
         cv = self._keys(vkeys, use_str)
         co = cv if okeys is vkeys else self._keys(okeys, use_str)
         self._bind_stream()
@@ -470,10 +596,13 @@ class B200(KVStoreBase):
                                                   C.byref(bid)))
         return BoundStep(self, bid.value, list(dict.fromkeys(vkeys)), (vals, outs, keep_v, keep_o))
 
-    def _view(self, key, which, shape=None):
+    def _view(self, key, which, shape=None, member=0):
         ck = self._keys([key], isinstance(key, str))
         p = C.c_void_p()
-        check_call(self._lib.b200kv_view(self._h, ck[0], which, C.byref(p)))
+        if self._members:
+            check_call(self._lib.b200kv_group_view(self._h, member, ck[0], which, C.byref(p)))
+        else:
+            check_call(self._lib.b200kv_view(self._h, ck[0], which, C.byref(p)))
         new = C.pythonapi.PyCapsule_New
         new.restype, new.argtypes = C.py_object, [C.c_void_p, C.c_char_p, C.c_void_p]
         t = torch.utils.dlpack.from_dlpack(new(p.value, b"dltensor", None))
@@ -495,18 +624,19 @@ class B200(KVStoreBase):
         """DLPack capsule of the key's gradient-bucket slot, for ``mx.nd.from_dlpack``."""
         return self._view_capsule(key, 1)
 
-    def weight_view(self, key, shape=None):
+    def weight_view(self, key, shape=None, member=0):
         """The stored weight of `key` as a zero-copy tensor.  A framework whose parameter array IS
-        this view (MXNet: ``mx.nd.from_dlpack``) needs no pull copy: pushpull updates it in place."""
-        return self._view(key, 0, shape)
+        this view (MXNet: ``mx.nd.from_dlpack``) needs no pull copy: pushpull updates it in place.
+        `member`: which device's copy, for a store that drives several GPUs."""
+        return self._view(key, 0, shape, member)
 
-    def grad_view(self, key, shape=None):
+    def grad_view(self, key, shape=None, member=0):
         """The slot of `key` in the gradient fusion bucket; gradients written here need no pack copy."""
-        return self._view(key, 1, shape)
+        return self._view(key, 1, shape, member)
 
-    def segment_views(self, key):
+    def segment_views(self, key, member=0):
         """(whole weight segment, whole gradient bucket) holding `key`, as flat tensors."""
-        return self._view(key, 2), self._view(key, 3)
+        return self._view(key, 2, None, member), self._view(key, 3, None, member)
 
     def set_profiling(self, enable):
         check_call(self._lib.b200kv_set_profiling(self._h, int(bool(enable))))
@@ -528,6 +658,9 @@ class B200(KVStoreBase):
         """kvstore.py:98-118 / base.py:77-95: init with rank 0's value, then pull into `out`."""
         vkeys, vals, use_str = _flatten(key, value)
         okeys, outs, _ = _flatten(key, out)
+        self._note(outs)
+        self._note(vals)
+        self._h                     # lazy mode: the out list names the devices (trainer.py:155-160)
         cv = self._keys(vkeys, use_str, create=True)
         co = self._keys(okeys, use_str)
         self._bind_stream()
@@ -557,6 +690,7 @@ class B200(KVStoreBase):
     def init_row_sparse(self, key, table):
         """Initialise a row-sparse key from the dense [num_rows, row_len] table holding all rows
         (what `w.tostype('row_sparse')` of a freshly initialised embedding is; trainer.py:155-157)."""
+        self._note([table])
         ck = self._keys([key], isinstance(key, str), create=True)
         self._bind_stream()
         ptrs, keep = self._handles([table], False)
@@ -607,6 +741,7 @@ class B200(KVStoreBase):
             keys = [key] * len(first_out)
         assert len(keys) == len(first_out) == len(row_ids), \
             "the number of row_ids doesn't match the number of values"
+        self._note(row_ids)
         ck = self._keys(keys, isinstance(keys[0], str))
         self._bind_stream()
         for k, c, o, ids in zip(keys, ck, first_out, row_ids):
@@ -614,8 +749,10 @@ class B200(KVStoreBase):
                 raise B200KVError("row_sparse_pull requires row_sparse outputs")
             shape = self._rsp_shapes[k]
             n = int(ids.numel()) if hasattr(ids, "numel") else int(ids.size)
-            idx = _empty((max(n, 1),), "int64", self._device)
-            val = _empty((max(n, 1),) + tuple(shape[1:]), "float32", self._device)
+            dev = _dev_index(ids)
+            dev = self._device if dev is None else dev     # the pulled rows land where the ids live
+            idx = _empty((max(n, 1),), "int64", dev)
+            val = _empty((max(n, 1),) + tuple(shape[1:]), "float32", dev)
             pr, k0 = self._handles([ids], False)
             pi, k1 = self._handles([idx], True)
             pd, k2 = self._handles([val], True)

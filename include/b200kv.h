@@ -217,10 +217,22 @@ int b200kv_rsp_merged_copy(b200kv_handle h, int key, DLManagedTensor* out_indice
 /* MXKVStorePullRowSparse (c_api.h:2868; kvstore_local.h:294-314,468-512; kvstore_utils.cu:44-110;
  * sparse_retain-inl.h:262-323): row_ids may be any shape / int or float dtype, unsorted, with
  * duplicates.  out_indices (int64) and out_values must hold at least numel(row_ids) rows;
- * *out_nnr receives the number of unique ids; rows absent from the store come back as zeros. */
+ * *out_nnr receives the number of unique ids; rows absent from the store come back as zeros.
+ * The call returns as soon as the count is known; the outputs are complete in stream order (like
+ * every other result of this library), not necessarily when the call returns.
+ * Row ids must lie in [0, num_rows): an id outside is an error (here, or — for ids of a push, which
+ * are checked on the device — at the next b200kv_row_sparse_pull / b200kv_wait). */
 int b200kv_row_sparse_pull(b200kv_handle h, int key, DLManagedTensor* row_ids,
                            DLManagedTensor* out_indices, DLManagedTensor* out_values,
                            int64_t* out_nnr, int priority);
+
+/* The same without the host synchronisation (the reference's UniqueImpl blocks on a device-to-host
+ * copy of the count, src/kvstore/kvstore_utils.cu:92-96): the number of unique ids is left in
+ * *out_nnr_dev (a DEVICE int64) in stream order; rows [nnr, numel(row_ids)) of the outputs are not
+ * written.  Row ids outside the table are reported by the next b200kv_wait. */
+int b200kv_row_sparse_pull_async(b200kv_handle h, int key, DLManagedTensor* row_ids,
+                                 DLManagedTensor* out_indices, DLManagedTensor* out_values,
+                                 int64_t* out_nnr_dev, int priority);
 
 /* MXKVStoreGetType / GetRank / GetGroupSize / Barrier (c_api.h:3029-3086) */
 int b200kv_get_type(b200kv_handle h, const char** out);

@@ -68,6 +68,7 @@ SIGNATURES = {
     "b200kv_rsp_merged_size": [_VP, _I, C.POINTER(_I64)],
     "b200kv_rsp_merged_copy": [_VP, _I, _VP, _VP],
     "b200kv_row_sparse_pull": [_VP, _I, _VP, _VP, _VP, C.POINTER(_I64), _I],
+    "b200kv_row_sparse_pull_async": [_VP, _I, _VP, _VP, _VP, _VP, _I],
     "b200kv_get_type": [_VP, C.POINTER(C.c_char_p)],
     "b200kv_get_rank": [_VP, _PI],
     "b200kv_get_group_size": [_VP, _PI],

@@ -289,6 +289,17 @@ int b200kv_row_sparse_pull(b200kv_handle h, int key, DLManagedTensor* row_ids,
   API_END();
 }
 
+int b200kv_row_sparse_pull_async(b200kv_handle h, int key, DLManagedTensor* row_ids,
+                                 DLManagedTensor* out_indices, DLManagedTensor* out_values,
+                                 int64_t* out_nnr_dev, int) {
+  API_BEGIN();
+  KV_CHECK(out_nnr_dev != nullptr, "out_nnr_dev must be a device pointer to one int64");
+  int64_t r = 0;
+  KVR(h, r, row_sparse_pull(key, row_ids, out_indices, out_values, out_nnr_dev));
+  (void)r;
+  API_END();
+}
+
 int b200kv_get_type(b200kv_handle h, const char** out) {
   API_BEGIN();
   *out = "b200";

@@ -369,12 +369,20 @@ void Group::init_rsp(int key, DLManagedTensor* dense_value) {
 void Group::push_rsp(int key, int ncopies, DLManagedTensor* const* idx, DLManagedTensor* const* val) {
   if (size() == 1) return m_[0]->push_rsp(key, ncopies, idx, val);
   // CommDevice::ReduceRowSparse (comm.h:478-501) gathers every copy on one device; here every member
-  // reduces ALL copies in list order (= the reference's device order), reading its siblings' rows
-  // through peer memory, and applies the identical update to its replica of the table
+  // reads ALL copies in list order (= the reference's device order), its siblings' through peer
+  // memory.  With an optimizer each member reduces and updates only the rows it owns (range-partitioned
+  // table and state); without one every member stores the identical merged value
   fence_in(true);
   for (auto& m : m_) {
     DeviceGuard g(m->device());
     m->push_rsp(key, ncopies, idx, val);
+  }
+  if (m_[0]->rsp_is_sharded(key)) {
+    // with an optimizer the table and its state are range-partitioned over the members (each one
+    // reduced and updated only the rows it owns); pulls gather from every member's shard
+    const float* tabs[kMaxCopies] = {nullptr};
+    for (int i = 0; i < size(); ++i) tabs[i] = m_[i]->rsp_table_ptr(key);
+    for (auto& m : m_) m->rsp_set_peer_tables(key, tabs);
   }
   fence_out();
 }
@@ -389,13 +397,18 @@ void Group::rsp_merged_copy(int key, DLManagedTensor* out_idx, DLManagedTensor* 
   CUDA_OK(cudaStreamSynchronize(m_[m]->stream()));
 }
 
-int64_t Group::row_sparse_pull(int key, DLManagedTensor* row_ids, DLManagedTensor* out_idx, DLManagedTensor* out_val) {
-  if (size() == 1) return m_[0]->row_sparse_pull(key, row_ids, out_idx, out_val);
+int64_t Group::row_sparse_pull(int key, DLManagedTensor* row_ids, DLManagedTensor* out_idx, DLManagedTensor* out_val,
+                               int64_t* nnr_dev) {
+  if (size() == 1) return m_[0]->row_sparse_pull(key, row_ids, out_idx, out_val, nnr_dev);
   KV_CHECK(out_val != nullptr, "row_sparse_pull values out: null DLManagedTensor");
   const int m = member_of_device(out_val->dl_tensor.device.device_id, 0);
   fence_in(true);
   DeviceGuard g(m_[m]->device());
-  return m_[m]->row_sparse_pull(key, row_ids, out_idx, out_val);   // blocks on the member's stream for the count
+  const int64_t n = m_[m]->row_sparse_pull(key, row_ids, out_idx, out_val, nnr_dev);   // sync form blocks for the count
+  // the host only waited for the count (if at all): the caller's stream picks up after the row gather
+  CUDA_OK(cudaEventRecord(ev_out_[m], own_[m]));
+  CUDA_OK(cudaStreamWaitEvent(caller_[m], ev_out_[m], 0));
+  return n;
 }
 
 }  // namespace b200kv

@@ -46,13 +46,14 @@ class Group : public KVHandle {
   void profile_read_phases(double ms[8], int64_t count[8]);
   int64_t launches() const;
   const char* last_exchange() const { return m_[0]->last_exchange(); }
-  // row sparse: replicated table; every member reduces all copies, reading its siblings' arrays
-  // through peer memory
+  // row sparse: every member reads all copies (its siblings' through peer memory); with an optimizer
+  // the table is range-partitioned over the members, each reducing / updating the rows it owns
   void init_rsp(int key, DLManagedTensor* dense_value);
   void push_rsp(int key, int ncopies, DLManagedTensor* const* idx, DLManagedTensor* const* val);
   int64_t rsp_merged_size(int key);
   void rsp_merged_copy(int key, DLManagedTensor* out_idx, DLManagedTensor* out_val);
-  int64_t row_sparse_pull(int key, DLManagedTensor* row_ids, DLManagedTensor* out_idx, DLManagedTensor* out_val);
+  int64_t row_sparse_pull(int key, DLManagedTensor* row_ids, DLManagedTensor* out_idx, DLManagedTensor* out_val,
+                          int64_t* nnr_dev = nullptr);
 
  private:
   struct Split {

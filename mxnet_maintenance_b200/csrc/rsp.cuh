@@ -270,6 +270,58 @@ struct RspUpdate {
   float* s1;
 };
 
+// the lazy row update of one element: table[o], s0[o], s1[o] <- gradient g
+template <int MODE>
+__device__ __forceinline__ void rsp_update_elem(const RspUpdate& up, int64_t o, float g) {
+  float w = up.table[o];
+  if (MODE == kRspSgd) {
+    if (up.has_mom) {
+      // SGDMomDnsRspDnsKernel (optimizer_op-inl.h:747-774): rate = lr*wd;
+      // mom = momentum*mom - rate*w - lr*clip(rescale*g) | lr*rescale*g;  w += mom
+      float mom = up.s0[o];
+      const float a = __fmul_rn(up.momentum, mom);
+      const float bb = __fmul_rn(__fmul_rn(up.lr, up.wd), w);
+      const float cc = up.clip >= 0.f ? __fmul_rn(up.lr, clipf(__fmul_rn(up.rescale, g), up.clip))
+                                      : __fmul_rn(__fmul_rn(up.lr, up.rescale), g);
+      mom = __fsub_rn(__fsub_rn(a, bb), cc);
+      up.s0[o] = mom;
+      up.table[o] = __fadd_rn(w, mom);
+    } else {
+      // SGDDnsRspKernel (optimizer_op-inl.h:452-475): (1 - lr*wd)*w - lr*clip(rescale*g) | (lr*rescale)*g
+      // — NOT the multi-tensor op's mom = 0 form, which rounds differently
+      const float keep = __fmul_rn(__fsub_rn(1.f, __fmul_rn(up.lr, up.wd)), w);
+      const float step = up.clip >= 0.f ? __fmul_rn(up.lr, clipf(__fmul_rn(up.rescale, g), up.clip))
+                                        : __fmul_rn(__fmul_rn(up.lr, up.rescale), g);
+      up.table[o] = __fsub_rn(keep, step);
+    }
+  } else if (MODE == kRspAdagrad) {
+    // AdagradDnsRspDnsKernel (optimizer_op-inl.h:2514-2539): h += g'^2; w -= g'/sqrt(h+eps) * lr
+    float gr = __fmul_rn(g, up.rescale);
+    if (up.clip >= 0.f) gr = clipf(gr, up.clip);
+    const float h = __fadd_rn(up.s0[o], __fmul_rn(gr, gr));
+    up.s0[o] = h;
+    const float div = __fdiv_rn(gr, __fsqrt_rn(__fadd_rn(h, up.eps)));
+    up.table[o] = __fsub_rn(w, __fmul_rn(div, up.lr));
+  } else if (MODE == kRspAdam) {
+    // AdamDnsRspDnsKernel<cpu> (optimizer_op-inl.h:1352-1382): note (1-beta2)*square(clip(g)) with
+    // clipping but (1-beta2)*g*g (left to right) without
+    float m = up.s0[o], v = up.s1[o];
+    float gr = __fadd_rn(__fmul_rn(g, up.rescale), __fmul_rn(w, up.wd));
+    const float omb1 = __fsub_rn(1.f, up.beta1), omb2 = __fsub_rn(1.f, up.beta2);
+    if (up.clip >= 0.f) {
+      gr = clipf(gr, up.clip);
+      m = __fadd_rn(__fmul_rn(up.beta1, m), __fmul_rn(omb1, gr));
+      v = __fadd_rn(__fmul_rn(up.beta2, v), __fmul_rn(omb2, __fmul_rn(gr, gr)));
+    } else {
+      m = __fadd_rn(__fmul_rn(up.beta1, m), __fmul_rn(omb1, gr));
+      v = __fadd_rn(__fmul_rn(up.beta2, v), __fmul_rn(__fmul_rn(omb2, gr), gr));
+    }
+    up.s0[o] = m;
+    up.s1[o] = v;
+    up.table[o] = __fsub_rn(w, __fdiv_rn(__fmul_rn(up.lr, m), __fadd_rn(__fsqrt_rn(v), up.eps)));
+  }
+}
+
 __device__ __forceinline__ const float* rsp_row(const RspInputs& in, uint32_t p, int64_t row_len) {
   int k = 0;
   while (k + 1 < in.n && static_cast<int64_t>(p) >= in.start[k + 1]) ++k;
@@ -309,45 +361,219 @@ rsp_reduce_kernel(const RspInputs in, const uint32_t* __restrict__ pay, const in
       } else {
         const int64_t o = row * row_len + c;
 #pragma unroll
-        for (int j = 0; j < W; ++j) {
-          float w = up.table[o + j];
-          if (MODE == kRspSgd) {
-            // SGDMomDnsRspDnsKernel: rate = lr*wd; mom = momentum*mom - rate*w - lr*clip(rescale*g) | lr*rescale*g
-            float mom = up.has_mom ? up.s0[o + j] : 0.f;
-            const float a = __fmul_rn(up.momentum, mom);
-            const float bb = __fmul_rn(__fmul_rn(up.lr, up.wd), w);
-            const float cc = up.clip >= 0.f ? __fmul_rn(up.lr, clipf(__fmul_rn(up.rescale, acc[j]), up.clip))
-                                            : __fmul_rn(__fmul_rn(up.lr, up.rescale), acc[j]);
-            mom = __fsub_rn(__fsub_rn(a, bb), cc);
-            if (up.has_mom) up.s0[o + j] = mom;
-            up.table[o + j] = __fadd_rn(w, mom);
-          } else if (MODE == kRspAdagrad) {
-            // AdagradDnsRspDnsKernel (optimizer_op-inl.h:2514-2539): h += g'^2; w -= g'/sqrt(h+eps) * lr
-            float gr = __fmul_rn(acc[j], up.rescale);
-            if (up.clip >= 0.f) gr = clipf(gr, up.clip);
-            const float h = __fadd_rn(up.s0[o + j], __fmul_rn(gr, gr));
-            up.s0[o + j] = h;
-            const float div = __fdiv_rn(gr, __fsqrt_rn(__fadd_rn(h, up.eps)));
-            up.table[o + j] = __fsub_rn(w, __fmul_rn(div, up.lr));
-          } else {
-            // AdamDnsRspDnsKernel<cpu>: note (1-beta2)*square(clip(g)) with clipping but
-            // (1-beta2)*g*g (left to right) without
-            float m = up.s0[o + j], v = up.s1[o + j];
-            float gr = __fadd_rn(__fmul_rn(acc[j], up.rescale), __fmul_rn(w, up.wd));
-            const float omb1 = __fsub_rn(1.f, up.beta1), omb2 = __fsub_rn(1.f, up.beta2);
-            if (up.clip >= 0.f) {
-              gr = clipf(gr, up.clip);
-              m = __fadd_rn(__fmul_rn(up.beta1, m), __fmul_rn(omb1, gr));
-              v = __fadd_rn(__fmul_rn(up.beta2, v), __fmul_rn(omb2, __fmul_rn(gr, gr)));
-            } else {
-              m = __fadd_rn(__fmul_rn(up.beta1, m), __fmul_rn(omb1, gr));
-              v = __fadd_rn(__fmul_rn(up.beta2, v), __fmul_rn(__fmul_rn(omb2, gr), gr));
-            }
-            up.s0[o + j] = m;
-            up.s1[o + j] = v;
-            up.table[o + j] = __fsub_rn(w, __fdiv_rn(__fmul_rn(up.lr, m), __fadd_rn(__fsqrt_rn(v), up.eps)));
-          }
+        for (int j = 0; j < W; ++j) rsp_update_elem<MODE>(up, o + j, acc[j]);
+      }
+    }
+  }
+}
+
+// =====================================================================================================
+// Bitmap path (tables up to 2^28 rows): the sorted unique set of row ids is a BITMAP over the row range
+// — 1M rows are 128 KB, resident in L2 — so "sort + unique" becomes  mark (atomicOr)  ->  one chained
+// popcount scan that also emits the ids in ascending order and clears the bitmap behind itself.
+// Pushed copies are sorted-unique already (row-sparse invariant), so the rows of an output id are
+// found by one binary search per copy inside the reduce kernel: no sort, no payload array.
+//   push, one copy   : 1 kernel  (the copy IS the merged index set)
+//   push, C copies   : mark + compact + reduce  = 3 kernels
+//   row_sparse_pull  : mark + compact + gather  = 3 kernels
+// (the radix-sort path above needs 10 / 20 launches and remains for tables beyond 2^28 rows)
+// =====================================================================================================
+constexpr int kMaxSources = 64;       // copies x ranks that one owner may reduce
+constexpr int kCompactWords = 1024;   // bitmap words per CTA of the compaction kernel (256 threads x 4)
+enum RspErr { kRspErrRange = 1, kRspErrOrder = 2 };
+
+struct RspSources {
+  const void* idx[kMaxSources];    // int64 row ids, sorted strictly ascending
+  const float* val[kMaxSources];   // [len, row_len]
+  int64_t len[kMaxSources];
+  // when set, the length is read from device memory instead (a peer rank's header word, written by
+  // that rank before the cross-GPU barrier that precedes the kernel)
+  const int64_t* len_ptr[kMaxSources];
+  int n;
+};
+__device__ __forceinline__ int64_t rsp_len(const RspSources& in, int k) {
+  return in.len_ptr[k] != nullptr ? __ldcv(in.len_ptr[k]) : in.len[k];
+}
+
+// ids -> bitmap bits for the rows in [row_lo, row_hi).  I: element type of the id arrays.
+template <typename I, bool CHECK_SORTED>
+__global__ void rsp_mark_kernel(const RspSources in, int64_t num_rows, int64_t row_lo, int64_t row_hi,
+                                uint32_t* __restrict__ bitmap, uint32_t* __restrict__ err) {
+  const int64_t stride = static_cast<int64_t>(gridDim.x) * blockDim.x;
+  for (int k = 0; k < in.n; ++k) {
+    const I* ids = static_cast<const I*>(in.idx[k]);
+    const int64_t len = rsp_len(in, k);
+    // the trip count is the same for every lane of a warp (i0 is the warp's lane-0 index), so the
+    // full-mask warp primitives below are legal
+    for (int64_t i0 = blockIdx.x * static_cast<int64_t>(blockDim.x) + (threadIdx.x & ~31); i0 < len;
+         i0 += stride) {
+      const int64_t i = i0 + (threadIdx.x & 31);
+      bool mine = i < len;
+      int64_t b = 0;
+      if (mine) {
+        const int64_t id = static_cast<int64_t>(ids[i]);
+        if (id < 0 || id >= num_rows) {
+          atomicOr(err, static_cast<uint32_t>(kRspErrRange));
+          mine = false;
+        } else {
+          if (CHECK_SORTED && i > 0 && static_cast<int64_t>(ids[i - 1]) >= id)
+            atomicOr(err, static_cast<uint32_t>(kRspErrOrder));
+          mine = id >= row_lo && id < row_hi;
+          b = id - row_lo;
         }
+      }
+      // duplicate-heavy id lists (Zipf) would hammer a few words with atomics: lanes that hit the same
+      // word merge their bits, and a word that already holds them is left alone
+      const uint32_t word = mine ? static_cast<uint32_t>(b >> 5) : 0xffffffffu;
+      const uint32_t bit = mine ? (1u << (b & 31)) : 0u;
+      const uint32_t peers = __match_any_sync(0xffffffffu, word);
+      const uint32_t bits = __reduce_or_sync(peers, bit);
+      if (mine && (__ffs(peers) - 1) == static_cast<int>(threadIdx.x & 31)) {
+        const uint32_t have = *reinterpret_cast<volatile uint32_t*>(bitmap + word);
+        if ((have & bits) != bits) atomicOr(&bitmap[word], bits);
+      }
+    }
+  }
+}
+
+// One-pass scan over the bitmap.  chain: 2 words per CTA {its count, epoch}; `epoch` differs on every
+// launch, so nothing is ever reset.
+// Emits the ids in ascending order, writes the total to count[0] and zeroes the bitmap.
+__global__ void __launch_bounds__(256)
+rsp_compact_kernel(uint32_t* __restrict__ bitmap, int nwords, int64_t row_lo, int64_t* __restrict__ uniq,
+                   int64_t* __restrict__ count, volatile uint32_t* chain, uint32_t epoch) {
+  __shared__ uint32_t ws[8];
+  __shared__ uint32_t s_prefix;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int w0 = blockIdx.x * kCompactWords + tid * 4;
+  uint32_t w[4] = {0u, 0u, 0u, 0u};
+  if (w0 < nwords) {   // the bitmap allocation is padded to whole CTAs
+    const uint4 v = *reinterpret_cast<const uint4*>(bitmap + w0);
+    w[0] = v.x; w[1] = v.y; w[2] = v.z; w[3] = v.w;
+    if (v.x | v.y | v.z | v.w) *reinterpret_cast<uint4*>(bitmap + w0) = make_uint4(0u, 0u, 0u, 0u);
+  }
+  const uint32_t c = __popc(w[0]) + __popc(w[1]) + __popc(w[2]) + __popc(w[3]);
+  uint32_t x = c;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    const uint32_t y = __shfl_up_sync(0xffffffffu, x, o);
+    if (lane >= o) x += y;
+  }
+  if (lane == 31) ws[warp] = x;
+  __syncthreads();
+  uint32_t before = x - c, total = 0;
+#pragma unroll
+  for (int k = 0; k < 8; ++k) {
+    if (k < warp) before += ws[k];
+    total += ws[k];
+  }
+  // publish this CTA's own count at once, then add up the counts of all CTAs before it: nobody waits
+  // for a prefix, only for counts that every CTA publishes right after loading its words — no serial
+  // chain (lower-numbered CTAs are scheduled first, so the waits always resolve)
+  if (tid == 0) {
+    chain[2 * blockIdx.x] = total;
+    __threadfence();
+    chain[2 * blockIdx.x + 1] = epoch;
+  }
+  uint32_t part = 0;
+  for (int j = tid; j < static_cast<int>(blockIdx.x); j += 256) {
+    while (chain[2 * j + 1] != epoch) {}
+    __threadfence();
+    part += chain[2 * j];
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) part += __shfl_down_sync(0xffffffffu, part, o);
+  __syncthreads();            // everyone has read ws[] of the first scan
+  if (lane == 0) ws[warp] = part;
+  __syncthreads();
+  if (tid == 0) {
+    uint32_t p = 0;
+#pragma unroll
+    for (int k = 0; k < 8; ++k) p += ws[k];
+    s_prefix = p;
+    if (blockIdx.x == gridDim.x - 1) count[0] = static_cast<int64_t>(p) + total;
+  }
+  __syncthreads();
+  int64_t pos = static_cast<int64_t>(s_prefix) + before;
+#pragma unroll
+  for (int j = 0; j < 4; ++j) {
+    uint32_t bits = w[j];
+    const int64_t base = row_lo + (static_cast<int64_t>(w0) + j) * 32;
+    while (bits) {
+      const int b = __ffs(bits) - 1;
+      uniq[pos++] = base + b;
+      bits &= bits - 1;
+    }
+  }
+}
+
+// One CTA per output row.  DIRECT: a single pushed copy — its index list is the merged set and source
+// row r is output row r.  Otherwise the row's id is looked up in every source by binary search
+// (thread k searches source k); rows are added in source order = the reference's device order
+// (ndarray_function.cc:81-113).  `up.table` / states start at row row_lo (this rank's shard).
+// MODE kRspStore: merged rows go to out_val[r], ids to out_idx[r], the row count to out_nnr.
+template <int MODE, bool VEC, bool DIRECT>
+__global__ void __launch_bounds__(128)
+rsp_reduce2_kernel(const RspSources in, const int64_t* __restrict__ uniq, const int64_t* __restrict__ count,
+                   int64_t row_len, int64_t num_rows, int64_t row_lo, int64_t row_hi, float* __restrict__ out_val,
+                   int64_t* __restrict__ out_idx, int64_t* __restrict__ out_nnr, const RspUpdate up,
+                   uint32_t* __restrict__ err) {
+  __shared__ int64_t s_pos[kMaxSources];
+  const int64_t nrows = DIRECT ? rsp_len(in, 0) : count[0];
+  if (MODE == kRspStore && blockIdx.x == 0 && threadIdx.x == 0 && out_nnr != nullptr) out_nnr[0] = nrows;
+  constexpr int W = VEC ? 4 : 1;
+  for (int64_t r = blockIdx.x; r < nrows; r += gridDim.x) {
+    int64_t row;
+    if (DIRECT) {
+      const int64_t* ids = static_cast<const int64_t*>(in.idx[0]);
+      row = ids[r];
+      bool bad = row < 0 || row >= num_rows;
+      if (bad && threadIdx.x == 0) atomicOr(err, static_cast<uint32_t>(kRspErrRange));
+      if (r > 0 && ids[r - 1] >= row) {   // duplicates would race on the table row
+        if (threadIdx.x == 0) atomicOr(err, static_cast<uint32_t>(kRspErrOrder));
+        bad = true;
+      }
+      if (bad || (MODE != kRspStore && (row < row_lo || row >= row_hi))) continue;
+    } else {
+      row = uniq[r];
+      __syncthreads();   // the previous row's readers are done with s_pos
+      for (int k = threadIdx.x; k < in.n; k += 128) {
+        const int64_t* ids = static_cast<const int64_t*>(in.idx[k]);
+        int64_t lo = 0, hi = rsp_len(in, k) - 1, found = -1;
+        while (lo <= hi) {
+          const int64_t m = lo + (hi - lo) / 2;
+          const int64_t v = ids[m];
+          if (v == row) { found = m; break; }
+          if (v < row) lo = m + 1; else hi = m - 1;
+        }
+        s_pos[k] = found;
+      }
+      __syncthreads();
+    }
+    if (MODE == kRspStore && threadIdx.x == 0) out_idx[r] = row;
+    for (int64_t c = static_cast<int64_t>(threadIdx.x) * W; c < row_len; c += 128 * W) {
+      float acc[W];
+#pragma unroll
+      for (int j = 0; j < W; ++j) acc[j] = 0.f;   // out = 0, then += every source row in order
+      for (int k = 0; k < in.n; ++k) {
+        const int64_t p = DIRECT ? r : s_pos[k];
+        if (p < 0) continue;
+        const float* src = in.val[k] + p * row_len + c;
+        if constexpr (VEC) {
+          const float4 v = *reinterpret_cast<const float4*>(src);
+          acc[0] = __fadd_rn(acc[0], v.x); acc[1] = __fadd_rn(acc[1], v.y);
+          acc[2] = __fadd_rn(acc[2], v.z); acc[3] = __fadd_rn(acc[3], v.w);
+        } else {
+          acc[0] = __fadd_rn(acc[0], src[0]);
+        }
+      }
+      if (MODE == kRspStore) {
+#pragma unroll
+        for (int j = 0; j < W; ++j) out_val[r * row_len + c + j] = acc[j];
+      } else {
+        const int64_t o = (row - row_lo) * row_len + c;
+#pragma unroll
+        for (int j = 0; j < W; ++j) rsp_update_elem<MODE>(up, o + j, acc[j]);
       }
     }
   }
@@ -356,10 +582,17 @@ rsp_reduce_kernel(const RspInputs in, const uint32_t* __restrict__ pay, const in
 // ---- row gather for row_sparse_pull ------------------------------------------------------------------
 // full != 0: the store holds every row (dense table); otherwise (src_idx, src_val) is a compact
 // row-sparse value and absent rows come back as zeros.
+// the table may be range-partitioned over the ranks: rows [o*rows_per_rank, (o+1)*rows_per_rank) live
+// in t[o] (peer memory for o != this rank); one GPU: t[0] holds everything
+struct RspTables {
+  const float* t[kMaxCopies];
+  int64_t rows_per_rank;
+};
+
 template <bool VEC>
 __global__ void __launch_bounds__(128)
 rsp_gather_kernel(const int64_t* __restrict__ uniq, const int64_t* __restrict__ count, int64_t row_len,
-                  int full, const float* __restrict__ table, int64_t num_rows,
+                  int full, const RspTables tabs, int64_t num_rows,
                   const int64_t* __restrict__ src_idx, const float* __restrict__ src_val,
                   const int64_t* __restrict__ src_nnr, int64_t* __restrict__ out_idx,
                   float* __restrict__ out_val) {
@@ -368,7 +601,10 @@ rsp_gather_kernel(const int64_t* __restrict__ uniq, const int64_t* __restrict__ 
     const int64_t id = uniq[r];
     const float* src = nullptr;
     if (full) {
-      if (id >= 0 && id < num_rows) src = table + id * row_len;
+      if (id >= 0 && id < num_rows) {
+        const int64_t o = id / tabs.rows_per_rank;
+        src = tabs.t[o] + (id - o * tabs.rows_per_rank) * row_len;
+      }
     } else {
       int64_t lo = 0, hi = src_nnr[0] - 1;
       while (lo <= hi) {

@@ -85,6 +85,7 @@ void Store::use_device() { CUDA_OK(cudaSetDevice(device_)); }
 void Store::wait() {
   use_device();
   CUDA_OK(cudaStreamSynchronize(stream_));
+  check_rsp_errors();
   // a peer that never arrived at a cross-GPU barrier leaves an error flag instead of a hung GPU
   for (auto& sp : segs_) {
     if (!sp->p2p.ok) continue;

@@ -119,8 +119,19 @@ class Store : public KVHandle {
   void push_rsp(int key, int ncopies, DLManagedTensor* const* idx, DLManagedTensor* const* val);
   int64_t rsp_merged_size(int key);
   void rsp_merged_copy(int key, DLManagedTensor* out_idx, DLManagedTensor* out_val);
+  // nnr_dev != nullptr: asynchronous — the unique-row count is left in that device int64, -1 returned
   int64_t row_sparse_pull(int key, DLManagedTensor* row_ids, DLManagedTensor* out_idx,
-                          DLManagedTensor* out_val);
+                          DLManagedTensor* out_val, int64_t* nnr_dev = nullptr);
+  // owner-sharded row-sparse keys (rsp.cu)
+  void shard_rsp_table(RspKey& k);
+  void setup_rsp_exchange(RspKey& k, int64_t rows_now, int ncopies);
+  void exchange_rsp_copies(RspKey& k, const struct RspInputs& in, int ncopies, struct RspSources* src, P2PFlags* bar);
+  // Group wiring: this member's shard, and its siblings' shards as seen from here
+  const float* rsp_table_ptr(int key);
+  bool rsp_is_sharded(int key);
+  void rsp_set_peer_tables(int key, const float* const* tables);
+  void check_rsp_error(RspKey& k, uint32_t bits);
+  void check_rsp_errors();
 
   // ---- used by Group (single process, several GPUs) -------------------------------------------------
   friend class Group;

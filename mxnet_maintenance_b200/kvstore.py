@@ -726,9 +726,11 @@ class B200(KVStoreBase):
         check_call(self._lib.b200kv_rsp_merged_copy(self._h, ck[0], pi[0], pd[0]))
         return RowSparse(val, idx, shape)
 
-    def row_sparse_pull(self, key, out=None, priority=0, row_ids=None):
+    def row_sparse_pull(self, key, out=None, priority=0, row_ids=None, sync=True):
         """kvstore.py:417-495: pulls the rows named by `row_ids` (any shape, unsorted, duplicates
-        allowed) into row-sparse `out`.  A single row_ids with a list of outs pulls once and copies."""
+        allowed) into row-sparse `out`.  A single row_ids with a list of outs pulls once and copies.
+        sync=False (extension): no host synchronisation — ``out.indices`` / ``out.data`` keep room for
+        numel(row_ids) rows and ``out.nnr`` is a 1-element device array holding how many are valid."""
         assert out is not None and row_ids is not None
         if _is_array(row_ids) and not isinstance(row_ids, (list, tuple)):
             row_ids = [row_ids]
@@ -756,6 +758,12 @@ class B200(KVStoreBase):
             pr, k0 = self._handles([ids], False)
             pi, k1 = self._handles([idx], True)
             pd, k2 = self._handles([val], True)
+            if not sync:
+                cnt = _empty((1,), "int64", dev)
+                check_call(self._lib.b200kv_row_sparse_pull_async(self._h, c, pr[0], pi[0], pd[0],
+                                                                  C.c_void_p(cnt.data_ptr()), priority))
+                o.indices, o.data, o.shape, o.nnr = idx, val, shape, cnt
+                continue
             nnr = C.c_int64()
             check_call(self._lib.b200kv_row_sparse_pull(self._h, c, pr[0], pi[0], pd[0], C.byref(nnr),
                                                         priority))

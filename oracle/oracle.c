@@ -331,6 +331,21 @@ int mxref_sgd_mom_rsp(int64_t nnr, int64_t row_len, float* out, float* mom, cons
   return 0;
 }
 
+/* SGDDnsRspKernel<req,cpu>::Map, optimizer_op-inl.h:452-475 — the momentum-free lazy update; note the
+ * (1 - lr*wd)*w form, which rounds differently from the multi-tensor op's mom = 0 form. */
+int mxref_sgd_rsp(int64_t nnr, int64_t row_len, float* out, const float* w, const int64_t* idx,
+                  const float* g, float clip, float lr, float wd, float rescale, int nthread) {
+#pragma omp parallel for num_threads(nthread)
+  for (int64_t i = 0; i < nnr; ++i) {
+    for (int64_t j = 0; j < row_len; ++j) {
+      int64_t di = idx[i] * row_len + j, gi = i * row_len + j;
+      if (clip >= 0.0f) out[di] = (1.f - lr * wd) * w[di] - (lr) * clipf(rescale * g[gi], clip);
+      else out[di] = (1.f - lr * wd) * w[di] - (lr * rescale) * g[gi];
+    }
+  }
+  return 0;
+}
+
 /* AdamDnsRspDnsKernel<req,cpu>::Map, optimizer_op-inl.h:1352-1382 */
 int mxref_adam_rsp(int64_t nnr, int64_t row_len, float* out, float* mean, float* var,
                    const float* w, const int64_t* idx, const float* g, float clip, float beta1,

@@ -90,6 +90,7 @@ class Oracle:
         L.mxref_multi_lars.argtypes = [C.c_int] + [C.c_void_p] * 5 + [fp] * 3
         L.mxref_multi_sum_sq.argtypes = [C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int]
         L.mxref_sgd_mom_rsp.argtypes = [C.c_int64, C.c_int64] + [C.c_void_p] * 5 + [fp] * 5 + [C.c_int]
+        L.mxref_sgd_rsp.argtypes = [C.c_int64, C.c_int64] + [C.c_void_p] * 4 + [fp] * 4 + [C.c_int]
         L.mxref_adam_rsp.argtypes = [C.c_int64, C.c_int64] + [C.c_void_p] * 6 + [fp] * 7 + [C.c_int]
         L.mxref_adagrad_rsp.argtypes = [C.c_int64, C.c_int64] + [C.c_void_p] * 5 + [fp] * 4 + [C.c_int]
         L.mxref_sparse_retain.argtypes = [C.c_int64] + [C.c_void_p] * 5 + [C.c_int64, C.c_int64]
@@ -213,6 +214,12 @@ class Oracle:
         self.lib.mxref_sgd_mom_rsp(len(idx), row_len, w.ctypes.data, mom.ctypes.data, w.ctypes.data,
                                    idx.ctypes.data, g.ctypes.data, clip, momentum, lr, wd, rescale,
                                    self.nthread)
+
+    def sgd_rsp(self, w, idx, g, lr, wd, rescale=1.0, clip=-1.0):
+        """sgd_update with a row-sparse gradient, lazy rows, no momentum (optimizer_op-inl.h:452-475)."""
+        row_len = w.shape[1]
+        self.lib.mxref_sgd_rsp(len(idx), row_len, w.ctypes.data, w.ctypes.data, idx.ctypes.data, g.ctypes.data,
+                               clip, lr, wd, rescale, self.nthread)
 
     def adam_rsp(self, w, mean, var, idx, g, lr, wd, beta1=0.9, beta2=0.999, eps=1e-8, rescale=1.0,
                  clip=-1.0):

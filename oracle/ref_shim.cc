@@ -351,6 +351,15 @@ int mxref_sgd_mom_rsp(int64_t nnr, int64_t row_len, float* out, float* mom, cons
   return 0;
 }
 
+// lazy row-sparse SGD without momentum (optimizer_op-inl.h:452-475)
+int mxref_sgd_rsp(int64_t nnr, int64_t row_len, float* out, const float* w, const int64_t* idx,
+                  const float* g, float clip, float lr, float wd, float rescale, int nthread) {
+#pragma omp parallel for num_threads(nthread)
+  for (int64_t i = 0; i < nnr; ++i)
+    SGDDnsRspKernel<kWriteTo, cpu>::Map<float, int64_t>(i, row_len, out, w, idx, g, clip, lr, wd, rescale);
+  return 0;
+}
+
 int mxref_adam_rsp(int64_t nnr, int64_t row_len, float* out, float* mean, float* var,
                    const float* w, const int64_t* idx, const float* g, float clip, float beta1,
                    float beta2, float lr, float wd, float eps, float rescale, int nthread) {

@@ -233,14 +233,18 @@ def test_group_views_and_bound_step(oracle):
     assert kv.launch_count() - base == 3 * 2          # one fused kernel per member per step
 
 
-def test_group_row_sparse(oracle):
+@pytest.mark.parametrize("devs", [[0, 0], [0] * 3, [0] * 4] + ([[0, 1]] if torch.cuda.device_count() >= 2 else []),
+                         ids=_ids)
+def test_group_row_sparse(oracle, devs):
     """Row-sparse key in a group: one row-sparse gradient per device, union-sum in device order
-    (ndarray_function.cc:81-113), lazy SGD-momentum rows, then row_sparse_pull."""
+    (ndarray_function.cc:81-113), lazy SGD-momentum rows, then row_sparse_pull.  With an optimizer the
+    table and its momentum are range-partitioned over the members (3000 rows over 3 members also
+    covers a ragged last shard)."""
     m = _mb()
-    num_rows, row_len = 3000, 64
+    num_rows, row_len = 3001, 64
     table = np.random.default_rng(3).uniform(-1, 1, (num_rows, row_len)).astype(np.float32)
     for with_opt in (False, True):
-        kv = m.B200(devices=[0, 0])
+        kv = m.B200(devices=devs)
         if with_opt:
             kv.set_optimizer(m.optimizer.SGD(learning_rate=0.1, momentum=0.9, wd=1e-3, rescale_grad=0.5))
         kv.init_row_sparse(0, torch.from_numpy(table).cuda())
@@ -248,11 +252,11 @@ def test_group_row_sparse(oracle):
         for step in range(2):
             rg = np.random.default_rng(900 + step)
             copies = []
-            for _ in range(2):
+            for _ in devs:
                 idx = np.unique(rg.integers(0, num_rows, 400)).astype(np.int64)
                 copies.append((idx, (rg.uniform(-1, 1, (len(idx), row_len)) * 1e-2).astype(np.float32)))
-            kv.push(0, [m.RowSparse(torch.from_numpy(v).cuda(), torch.from_numpy(i).cuda(), (num_rows, row_len))
-                        for i, v in copies])
+            kv.push(0, [m.RowSparse(torch.from_numpy(v).to("cuda:%d" % d), torch.from_numpy(i).to("cuda:%d" % d),
+                                    (num_rows, row_len)) for (i, v), d in zip(copies, devs)])
             midx, mval = oracle.rsp_sum(copies)
             if with_opt:
                 oracle.sgd_mom_rsp(ref, mom, midx, mval, 0.1, 1e-3, 0.9, 0.5)
@@ -261,9 +265,10 @@ def test_group_row_sparse(oracle):
                 assert mg.indices.cpu().numpy().tobytes() == midx.tobytes()
                 assert mg.data.cpu().numpy().tobytes() == mval.tobytes()
         if with_opt:
-            out = m.RowSparse(None, None, (0, 0))
-            kv.row_sparse_pull(0, out=out, row_ids=torch.arange(num_rows, device="cuda"))
-            assert out.data.cpu().numpy().tobytes() == ref.tobytes()
+            for d in sorted(set(devs)):         # any device may pull: rows come from every member's shard
+                out = m.RowSparse(None, None, (0, 0))
+                kv.row_sparse_pull(0, out=out, row_ids=torch.arange(num_rows, device="cuda:%d" % d))
+                assert out.data.cpu().numpy().tobytes() == ref.tobytes()
 
 
 def test_group_save_load_states(tmp_path, oracle):

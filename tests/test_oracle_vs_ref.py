@@ -130,6 +130,8 @@ def test_row_sparse_kernels(oracle, oracle_ref):
         hh = np.zeros_like(W)
         o.adagrad_rsp(ww, hh, idx, gg, 0.1)
         o.adagrad_rsp(ww, hh, idx, gg, 0.1, rescale=0.5, clip=0.2)
+        o.sgd_rsp(ww, idx, gg, 0.1, 1e-3)                       # SGDDnsRspKernel: (1 - lr*wd)*w form
+        o.sgd_rsp(ww, idx, gg, 0.1, 1e-3, 0.5, 0.1)
         return np.concatenate([ww.ravel(), mm.ravel(), me.ravel(), va.ravel(), hh.ravel()])
     a, b = _both(oracle, oracle_ref, f)
     assert a.tobytes() == b.tobytes()

@@ -113,7 +113,10 @@ def test_lazy_row_update(oracle, kind):
         grads = _grads(rng, num_rows, row_len, 4, 500)
         _push(kv, mb, grads)
         midx, mval = oracle.rsp_sum(grads)
-        if kind.startswith("sgd"):
+        if kind.startswith("sgd") and mom == 0.0:
+            # momentum-free sparse SGD is SGDDnsRspKernel: (1 - lr*wd)*w - lr*g (optimizer_op-inl.h:452-475)
+            oracle.sgd_rsp(ref, midx, mval, 0.1, 1e-3, 0.5, clip if clip else -1.0)
+        elif kind.startswith("sgd"):
             oracle.sgd_mom_rsp(ref, s0, midx, mval, 0.1, 1e-3, mom, 0.5, clip if clip else -1.0)
         elif kind.startswith("adagrad"):
             oracle.adagrad_rsp(ref, s0, midx, mval, 0.05, 1e-7, 0.5, clip if clip else -1.0)
@@ -180,3 +183,45 @@ def test_pull_with_millions_of_ids(oracle):
         uniq = np.unique(ids).astype(np.int64)
         assert pi.tobytes() == uniq.tobytes()
         assert pv.tobytes() == table[uniq].tobytes()
+
+
+def test_row_ids_are_validated(oracle):
+    """A pushed id outside the table (or an unsorted / duplicated index list) must not corrupt memory:
+    the rows are skipped on the device and the fault is reported at the next synchronisation point;
+    a pulled id outside the table is an error."""
+    import mxnet_maintenance_b200 as mb0
+    rng = np.random.default_rng(9)
+    num_rows, row_len = 1000, 8
+    table = rng.uniform(-1, 1, (num_rows, row_len)).astype(np.float32)
+    for ncopies in (1, 2):
+        kv, mb = _kv(table, mb0.optimizer.SGD(learning_rate=0.1))
+        good = (np.array([1, 5, 9], np.int64), np.ones((3, row_len), np.float32))
+        bad = (np.array([2, 7, num_rows + 3], np.int64), np.ones((3, row_len), np.float32))
+        _push(kv, mb, [good, bad][:ncopies] if ncopies == 2 else [bad])
+        with pytest.raises(mb.B200KVError, match="outside"):
+            kv.wait()
+        kv.wait()                                       # reported once
+        unsorted = (np.array([9, 5, 5], np.int64), np.ones((3, row_len), np.float32))
+        _push(kv, mb, [unsorted] + ([good] if ncopies == 2 else []))
+        with pytest.raises(mb.B200KVError, match="sorted and unique"):
+            kv.wait()
+        with pytest.raises(mb.B200KVError, match="outside"):
+            _pull(kv, mb, torch.tensor([3, num_rows], device="cuda"))
+        pi, pv = _pull(kv, mb, torch.tensor([0, 999], device="cuda"))     # untouched rows are intact
+        assert pi.tolist() == [0, 999] and pv.tobytes() == table[[0, 999]].tobytes()
+
+
+def test_row_sparse_pull_async(oracle):
+    """sync=False leaves the unique-row count on the device (no host synchronisation in the call)."""
+    rng = np.random.default_rng(11)
+    num_rows, row_len = 4099, 32
+    table = rng.uniform(-1, 1, (num_rows, row_len)).astype(np.float32)
+    kv, mb = _kv(table)
+    ids = rng.integers(0, num_rows, 5000)
+    out = mb.RowSparse(None, None, (0, 0))
+    kv.row_sparse_pull(0, out=out, row_ids=torch.from_numpy(ids).cuda(), sync=False)
+    n = int(out.nnr.item())
+    uniq = np.unique(ids).astype(np.int64)
+    assert n == len(uniq)
+    assert out.indices[:n].cpu().numpy().tobytes() == uniq.tobytes()
+    assert out.data[:n].cpu().numpy().tobytes() == table[uniq].tobytes()

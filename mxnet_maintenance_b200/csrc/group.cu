@@ -68,6 +68,9 @@ Group::Group(int ndev, const int* dev_ids) {
 }
 
 Group::~Group() {
+  int prev = 0;
+  cudaGetDevice(&prev);
+  struct Restore { int d; ~Restore() { cudaSetDevice(d); } } restore{prev};   // the caller's current device stays
   for (size_t i = 0; i < m_.size(); ++i) {
     cudaSetDevice(m_[i]->device());
     if (own_[i]) cudaStreamSynchronize(own_[i]);

@@ -60,6 +60,9 @@ Store::Store(int device, int rank, int world, bool in_process, int grid_share)
 }
 
 Store::~Store() {
+  int prev = 0;
+  cudaGetDevice(&prev);
+  struct Restore { int d; ~Restore() { cudaSetDevice(d); } } restore{prev};   // the caller's current device stays
   cudaSetDevice(device_);
   cudaStreamSynchronize(stream_);
   for (auto& sp : segs_) {   // unmap the peers' buffers before our own are freed

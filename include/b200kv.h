@@ -174,6 +174,11 @@ typedef struct {
   float lower_bound, upper_bound;      /* LAMB; < 0: off */
   float clip_global_norm;              /* gluon.utils.clip_global_norm max_norm applied to the
                                           merged gradients of one push; < 0: off */
+  int32_t std_update;                  /* row-sparse keys: 0 = lazy update, only the rows of the gradient
+                                          (lazy_update=True, the reference's default); 1 = standard update
+                                          of EVERY row, absent rows with a zero gradient (lazy_update=False:
+                                          SGDMomStdDnsRspDnsKernel / AdamStdDnsRspDnsKernel,
+                                          src/operator/optimizer_op.cc:108-286) */
 } b200kv_optimizer;
 int b200kv_set_optimizer(b200kv_handle h, const b200kv_optimizer* opt);
 /* per-key scalars for the next update: learning rate (for Adam already bias-corrected, as
@@ -274,6 +279,22 @@ int b200kv_multi_sgd_update(int num, int dtype, void* const* weights, const void
                             float* const* moms, float* const* weights32, const int64_t* sizes,
                             const float* lrs, const float* wds, float momentum, float rescale_grad,
                             float clip_gradient, void* stream);
+/* sgd_update / mp_sgd_update (src/operator/optimizer_op-inl.h:382-419,656-699): the single-tensor,
+ * momentum-free form (1 - lr*wd)*w - lr*clip(rescale*g) — its rounding differs from the multi-tensor
+ * op's mom = 0 form, which is why it is a separate entry point.  dtype 2: fp16 weight / grad with the
+ * fp32 master `weight32` (mp_sgd_update); weight32 is ignored for dtype 0. */
+int b200kv_sgd_update(int dtype, void* weight, const void* grad, float* weight32, int64_t size, float lr,
+                      float wd, float rescale_grad, float clip_gradient, void* stream);
+/* lamb_update_phase1 / lamb_update_phase2 (src/operator/optimizer_op-inl.h:1567-1763; Python
+ * optimizer.py:1275-1315), fp32: phase 1 updates mean / var and writes the update direction to g_out;
+ * the caller computes r1 = ||weight||, r2 = ||g_out|| (e.g. sqrt of b200kv_multi_sum_sq) and hands
+ * them to phase 2 as DEVICE scalars.  The multi-precision variants are not provided: the reference's
+ * MPLambUpdatePhaseTwoKernel never writes weight32 back (:1863-1886). */
+int b200kv_lamb_update_phase1(float* g_out, const float* weight, const float* grad, float* mean, float* var,
+                              int64_t size, float beta1, float beta2, float epsilon, int t, int bias_correction,
+                              float wd, float rescale_grad, float clip_gradient, void* stream);
+int b200kv_lamb_update_phase2(float* weight, const float* g, const float* r1, const float* r2, int64_t size,
+                              float lr, float lower_bound, float upper_bound, void* stream);
 /* adam_update over a tensor list (optimizer_op-inl.h:1252-1340); dtype 2 is the fused form of
  * the multi-precision wrapper (optimizer.py:298-304). */
 int b200kv_multi_adam_update(int num, int dtype, void* const* weights, const void* const* grads,

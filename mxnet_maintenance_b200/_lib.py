@@ -21,7 +21,7 @@ class OptimizerDesc(C.Structure):
                 ("momentum", C.c_float), ("beta1", C.c_float), ("beta2", C.c_float),
                 ("epsilon", C.c_float), ("rescale_grad", C.c_float), ("clip_gradient", C.c_float),
                 ("lower_bound", C.c_float), ("upper_bound", C.c_float),
-                ("clip_global_norm", C.c_float)]
+                ("clip_global_norm", C.c_float), ("std_update", C.c_int32)]
 
 
 OPT_NONE, OPT_SGD, OPT_ADAM, OPT_LAMB, OPT_ADAGRAD = 0, 1, 2, 3, 4
@@ -77,6 +77,9 @@ SIGNATURES = {
     "b200kv_launch_count": [_VP, C.POINTER(_I64)],
     "b200kv_multi_sgd_update": [_I, _I, _PVP, _PVP, _PVP, _PVP, C.POINTER(_I64), _PF, _PF, _F, _F,
                                 _F, _VP],
+    "b200kv_sgd_update": [_I, _VP, _VP, _VP, _I64, _F, _F, _F, _F, _VP],
+    "b200kv_lamb_update_phase1": [_VP, _VP, _VP, _VP, _VP, _I64, _F, _F, _F, _I, _I, _F, _F, _F, _VP],
+    "b200kv_lamb_update_phase2": [_VP, _VP, _VP, _VP, _I64, _F, _F, _F, _VP],
     "b200kv_multi_adam_update": [_I, _I, _PVP, _PVP, _PVP, _PVP, _PVP, C.POINTER(_I64), _PF, _PF,
                                  _F, _F, _F, _F, _F, _VP],
     "b200kv_multi_lamb_update": [_I, _I, _PVP, _PVP, _PVP, _PVP, _PVP, C.POINTER(_I64), _PF, _PF,

@@ -458,6 +458,85 @@ int b200kv_multi_sgd_update(int num, int dtype, void* const* weights, const void
   API_END();
 }
 
+int b200kv_sgd_update(int dtype, void* weight, const void* grad, float* weight32, int64_t size, float lr,
+                      float wd, float rescale_grad, float clip_gradient, void* stream) {
+  API_BEGIN();
+  if (size <= 0) return 0;
+  const int dev = current_device();
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  OpWorkspace& w = workspace(dev, stream);
+  std::lock_guard<std::mutex> lk(w.mu);
+  prepare_plan(w, 1, &size, st);
+  void* ws[1] = {weight};
+  const void* gs[1] = {grad};
+  float* w32[1] = {weight32};
+  MtaCall c = make_call(w, 1, dtype, ws, gs, nullptr, nullptr, dtype == kF16 ? w32 : nullptr, &lr, &wd, nullptr,
+                        nullptr, st, dev);
+  OptScalars s;
+  s.rescale = rescale_grad; s.clip = clip_gradient;
+  launch_sgd_plain(c, s);
+  w.ring.end(st);
+  API_END();
+}
+
+int b200kv_lamb_update_phase1(float* g_out, const float* weight, const float* grad, float* mean, float* var,
+                              int64_t size, float beta1, float beta2, float epsilon, int t, int bias_correction,
+                              float wd, float rescale_grad, float clip_gradient, void* stream) {
+  API_BEGIN();
+  if (size <= 0) return 0;
+  KV_CHECK(g_out && weight && grad && mean && var, "null array");
+  const int dev = current_device();
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  OpWorkspace& w = workspace(dev, stream);
+  std::lock_guard<std::mutex> lk(w.mu);
+  prepare_plan(w, 1, &size, st);
+  Table tb{w.ring.begin(mta_blob_words(1, 1, 0) * 8), 1, 1, 0};
+  std::memset(tb.p, 0, mta_blob_words(1, 1, 0) * 8);
+  tb.G(0, 0, grad);
+  tb.Sx(kSecW, 0, weight);
+  tb.Sx(kSecS0, 0, mean);
+  tb.Sx(kSecS1, 0, var);
+  tb.Sx(kSecX, 0, g_out);
+  tb.F2(kSecLrWd, 0, 0.f, wd);
+  // DType beta1_t = std::pow(param.beta1, param.t) (optimizer_op-inl.h:1661-1662): double pow, rounded to float
+  tb.F2(kSecAux, 0, static_cast<float>(std::pow(static_cast<double>(beta1), static_cast<double>(t))),
+        static_cast<float>(std::pow(static_cast<double>(beta2), static_cast<double>(t))));
+  MtaCall c;
+  c.blob = w.ring.commit(st);
+  c.plan = w.plan;
+  c.nt = 1; c.ngrad = 1; c.nout = 0; c.dtype = kF32; c.stream = st; c.device = dev;
+  OptScalars s;
+  s.beta1 = beta1; s.beta2 = beta2; s.eps = epsilon; s.rescale = rescale_grad; s.clip = clip_gradient;
+  s.bias_correction = bias_correction;
+  launch_lamb_phase1(c, s);
+  w.ring.end(st);
+  API_END();
+}
+
+int b200kv_lamb_update_phase2(float* weight, const float* g, const float* r1, const float* r2, int64_t size,
+                              float lr, float lower_bound, float upper_bound, void* stream) {
+  API_BEGIN();
+  if (size <= 0) return 0;
+  KV_CHECK(weight && g && r1 && r2, "null array");
+  const int dev = current_device();
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  OpWorkspace& w = workspace(dev, stream);
+  std::lock_guard<std::mutex> lk(w.mu);
+  prepare_plan(w, 1, &size, st);
+  Table tb{w.ring.begin(mta_blob_words(1, 1, 0) * 8), 1, 1, 0};
+  std::memset(tb.p, 0, mta_blob_words(1, 1, 0) * 8);
+  tb.Sx(kSecW, 0, weight);
+  tb.Sx(kSecX, 0, g);
+  tb.F2(kSecLrWd, 0, lr, 0.f);
+  MtaCall c;
+  c.blob = w.ring.commit(st);
+  c.plan = w.plan;
+  c.nt = 1; c.ngrad = 1; c.nout = 0; c.dtype = kF32; c.stream = st; c.device = dev;
+  launch_lamb_phase2(c, r1, r2, lower_bound, upper_bound);
+  w.ring.end(st);
+  API_END();
+}
+
 int b200kv_multi_adam_update(int num, int dtype, void* const* weights, const void* const* grads,
                              float* const* means, float* const* vars, float* const* weights32,
                              const int64_t* sizes, const float* lrs, const float* wds, float beta1,

@@ -33,6 +33,10 @@ struct OptScalars {
 // Update kernels: W section is the fp32 weight (dtype kF32) or the fp32 master (dtype kF16).
 int launch_sgd(const MtaCall& c, bool has_mom, const OptScalars& s, const float* gscale);
 int launch_adam(const MtaCall& c, const OptScalars& s, const float* gscale);
+// single-tensor forms: sgd_update / mp_sgd_update, lamb_update_phase1 / phase2 (fp32)
+int launch_sgd_plain(const MtaCall& c, const OptScalars& s);
+int launch_lamb_phase1(const MtaCall& c, const OptScalars& s);
+int launch_lamb_phase2(const MtaCall& c, const float* r1, const float* r2, float lower, float upper);
 int launch_adagrad(const MtaCall& c, const OptScalars& s, const float* gscale);
 int launch_adamw(const MtaCall& c, const OptScalars& s, const float* rescale_dev);
 // partials [nchunks]: number of non-finite values per chunk

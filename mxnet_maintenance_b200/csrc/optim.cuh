@@ -352,6 +352,75 @@ static __global__ void all_finite_final_kernel(const float* __restrict__ sums, i
   }
 }
 
+// sgd_update / mp_sgd_update: SGDKernel / MP_SGDKernel (src/operator/optimizer_op-inl.h:382-399,
+// 656-679) — the momentum-free single-tensor form (1 - lr*wd)*w - lr*clip(rescale*g) | (lr*rescale)*g,
+// which rounds differently from MultiSGDKernel's mom = 0 form
+struct SgdPlainOp {
+  static constexpr OpFlags F = {true, true, true, true, false, false, false, false, 0};
+  float rescale, clip;
+  struct PT { float lr, keep, lrrs; };
+  __device__ __forceinline__ PT prep(float lr, float wd, float, float) const {
+    return {lr, __fsub_rn(1.f, __fmul_rn(lr, wd)), __fmul_rn(lr, rescale)};
+  }
+  template <typename T>
+  __device__ __forceinline__ void elem(const PT& p, float& w, float g, float&, float&, float*) const {
+    const float step = clip >= 0.0f ? __fmul_rn(p.lr, clipf(__fmul_rn(rescale, g), clip)) : __fmul_rn(p.lrrs, g);
+    w = __fsub_rn(__fmul_rn(p.keep, w), step);
+  }
+};
+
+// lamb_update_phase1: LambUpdatePhaseOneKernel (optimizer_op-inl.h:1622-1649), fp32.  aux0 / aux1 =
+// beta1^t / beta2^t (std::pow on the host, :1661-1662).  Note the reference's `1.` literal: the
+// mean's bias correction divides in DOUBLE, the variance's in float.  The update direction g goes to
+// the X section.
+struct LambPhase1Op {
+  static constexpr OpFlags F = {true, true, false, false, true, true, true, true, 0, false, true};
+  float beta1, beta2, eps, rescale, clip;
+  int bias_correction;
+  struct PT { float wd, b1t, b2t, omb1, omb2; };
+  __device__ __forceinline__ PT prep(float, float wd, float a0, float a1) const {
+    return {wd, a0, a1, __fsub_rn(1.f, beta1), __fsub_rn(1.f, beta2)};
+  }
+  template <typename T>
+  __device__ __forceinline__ void elem(const PT& p, float& w, float g, float& m, float& v, float* red) const {
+    float gr = __fmul_rn(g, rescale);
+    if (clip >= 0.f) gr = clipf(gr, clip);
+    m = __fadd_rn(__fmul_rn(beta1, m), __fmul_rn(p.omb1, gr));
+    v = __fadd_rn(__fmul_rn(beta2, v), __fmul_rn(__fmul_rn(p.omb2, gr), gr));
+    float u;
+    if (bias_correction) {
+      const float mh = static_cast<float>(__ddiv_rn(static_cast<double>(m), __dsub_rn(1.0, static_cast<double>(p.b1t))));
+      const float vh = __fdiv_rn(v, __fsub_rn(1.f, p.b2t));
+      u = __fadd_rn(__fdiv_rn(mh, __fadd_rn(__fsqrt_rn(vh), eps)), __fmul_rn(p.wd, w));
+    } else {
+      u = __fadd_rn(__fdiv_rn(m, __fadd_rn(__fsqrt_rn(v), eps)), __fmul_rn(p.wd, w));
+    }
+    red[kXSlot] = u;
+  }
+};
+
+// lamb_update_phase2: LambUpdatePhaseTwoKernel (optimizer_op-inl.h:1706-1730): r1, r2 are DEVICE
+// scalars (the norms of weight and g); lr' = lr * clamp(r1) / r2 unless either is 0; w -= lr' * g
+struct LambPhase2Op {
+  static constexpr OpFlags F = {false, true, true, true, false, false, false, false, 0, true, false};
+  const float* r1;
+  const float* r2;
+  float lower, upper;
+  struct PT { float lr; };
+  __device__ __forceinline__ PT prep(float lr, float, float, float) const {
+    float n1 = *r1;
+    const float n2 = *r2;
+    if (lower >= 0.f) n1 = fmaxf(n1, lower);
+    if (upper >= 0.f) n1 = fminf(n1, upper);
+    if (!(n1 == 0.0f || n2 == 0.0f)) lr = __fdiv_rn(__fmul_rn(lr, n1), n2);
+    return {lr};
+  }
+  template <typename T>
+  __device__ __forceinline__ void elem(const PT& p, float& w, float, float&, float&, float* red) const {
+    w = __fsub_rn(w, __fmul_rn(p.lr, red[kXSlot]));
+  }
+};
+
 // AdaGrad, dense branch of AdaGrad.update (python/mxnet/optimizer/optimizer.py:1681-1687), the same
 // chain of fp32 operations the NDArray expressions perform:
 //   g = g*rescale; clip; history += g*g; div = g / sqrt(history + eps); w += (div + w*wd) * -lr

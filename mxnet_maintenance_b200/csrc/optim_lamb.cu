@@ -22,6 +22,23 @@ int launch_lamb2(const MtaCall& c, const OptScalars& s, const float* ratio) {
   return launch_update(c, op, nullptr, nullptr);
 }
 
+int launch_sgd_plain(const MtaCall& c, const OptScalars& s) {
+  SgdPlainOp op{s.rescale, s.clip};
+  return launch_update(c, op, nullptr, nullptr);
+}
+
+int launch_lamb_phase1(const MtaCall& c, const OptScalars& s) {
+  KV_CHECK(c.dtype == kF32, "lamb_update_phase1 is float32");
+  LambPhase1Op op{s.beta1, s.beta2, s.eps, s.rescale, s.clip, s.bias_correction};
+  return launch_ng<LambPhase1Op, float, float>(c, op, nullptr, nullptr);
+}
+
+int launch_lamb_phase2(const MtaCall& c, const float* r1, const float* r2, float lower, float upper) {
+  KV_CHECK(c.dtype == kF32, "lamb_update_phase2 is float32");
+  LambPhase2Op op{r1, r2, lower, upper};
+  return launch_ng<LambPhase2Op, float, float>(c, op, nullptr, nullptr);
+}
+
 int launch_sumsq(const MtaCall& c, float* partials) {
   SumSqOp op;
   if (c.dtype == kF32) return launch_ng<SumSqOp, float, float>(c, op, nullptr, partials);

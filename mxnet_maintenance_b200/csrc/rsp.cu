@@ -484,6 +484,20 @@ void Store::push_rsp(int key, int ncopies, DLManagedTensor* const* idx, DLManage
     up.has_mom = opt_.kind == B200KV_OPT_SGD && opt_.momentum != 0.f;
     up.table = k.table.as<float>(); up.s0 = k.s0.as<float>(); up.s1 = k.s1.as<float>();
     up.mode = opt_.kind == B200KV_OPT_SGD ? kRspSgd : (opt_.kind == B200KV_OPT_ADAM ? kRspAdam : kRspAdagrad);
+    // lazy_update=False: every row is updated (there is no standard form of the sparse AdaGrad op)
+    up.std_update = opt_.std_update != 0 && opt_.kind != B200KV_OPT_ADAGRAD;
+    if (up.std_update) {
+      KV_CHECK(k.use_bitmap(), "the standard (non-lazy) row-sparse update is limited to tables of 2^28 rows");
+      // (between processes the peers' row counts are only known on the device: room for the whole shard)
+      const int64_t room = std::max<int64_t>(1, exchange ? k.rows_per_rank
+                                                         : (k.sharded ? std::min<int64_t>(k.rows_per_rank, total) : total));
+      if (room > k.c_cap) {   // the merged gradient is staged where an updater-less push keeps its value
+        k.c_cap = room;
+        k.c_idx.reserve(8 * static_cast<size_t>(room));
+        k.c_val.reserve(4 * static_cast<size_t>(room) * k.row_len);
+      }
+      k.c_nnr.reserve(8);
+    }
   }
   const bool vec = (k.row_len % 4) == 0;   // cudaMalloc'd tables and DLPack row blocks are 16-B aligned
   const int nn = static_cast<int>(total);
@@ -513,7 +527,7 @@ void Store::push_rsp(int key, int ncopies, DLManagedTensor* const* idx, DLManage
       if (k.sharded) bound = std::min<int64_t>(k.rows_per_rank, total);
     }
     k.reserve_uniq(std::max<int64_t>(bound, 1));
-    const bool direct = src.n == 1 && !k.sharded;
+    const bool direct = src.n == 1 && !k.sharded && !up.std_update;
     if (!direct) {
       k.ensure_bitmap();
       const int g = static_cast<int>(std::max<int64_t>(1, std::min<int64_t>((maxlen + 255) / 256, sm_count(device_) * 4)));
@@ -525,9 +539,31 @@ void Store::push_rsp(int key, int ncopies, DLManagedTensor* const* idx, DLManage
     }
     const int grid = static_cast<int>(std::max<int64_t>(
         1, std::min<int64_t>(exchange ? bound : (direct ? maxlen : total), sm_count(device_) * 16)));
-    float* ov = upd ? nullptr : k.c_val.as<float>();
-    int64_t* oi = upd ? nullptr : k.c_idx.as<int64_t>();
-    int64_t* on = upd ? nullptr : k.c_nnr.as<int64_t>();
+    const bool stage = !upd || up.std_update;
+    float* ov = stage ? k.c_val.as<float>() : nullptr;
+    int64_t* oi = stage ? k.c_idx.as<int64_t>() : nullptr;
+    int64_t* on = stage ? k.c_nnr.as<int64_t>() : nullptr;
+    if (up.std_update) {
+      // merged rows first (sum in device order), then one pass over EVERY row of this rank's shard
+      if (exchange) KV_CHECK(bound <= k.c_cap, "internal: staging too small for the standard update");
+      launch_reduce2<kRspStore>(vec, false, grid, stream_, src, k, k.row_lo, k.row_hi, ov, oi, on, up);
+      const int g2 = static_cast<int>(std::max<int64_t>(1, std::min<int64_t>(k.row_hi - k.row_lo, sm_count(device_) * 16)));
+#define STD(MODE)                                                                                             \
+  do {                                                                                                        \
+    if (vec) rsp_std_update_kernel<MODE, true><<<g2, 128, 0, stream_>>>(oi, on, ov, k.row_len, k.row_lo, k.row_hi, up);  \
+    else rsp_std_update_kernel<MODE, false><<<g2, 128, 0, stream_>>>(oi, on, ov, k.row_len, k.row_lo, k.row_hi, up);     \
+  } while (0)
+      if (up.mode == kRspSgd) STD(kRspSgd);
+      else STD(kRspAdam);
+#undef STD
+      CUDA_OK(cudaGetLastError());
+      launches_ += 2;
+      if (exchange) {
+        bar.epoch = k.x.epoch;
+        launches_ += launch_p2p_barrier(bar, 1, stream_);
+      }
+      return;
+    }
     switch (up.mode) {
       case kRspStore: launch_reduce2<kRspStore>(vec, direct, grid, stream_, src, k, k.row_lo, k.row_hi, ov, oi, on, up); break;
       case kRspSgd: launch_reduce2<kRspSgd>(vec, direct, grid, stream_, src, k, k.row_lo, k.row_hi, ov, oi, on, up); break;

@@ -265,6 +265,7 @@ struct RspUpdate {
   int mode;
   float lr, wd, momentum, beta1, beta2, eps, rescale, clip;
   int has_mom;
+  int std_update;   // standard (non-lazy) update: every row is updated, Adam squares the whole gradient term
   float* table;  // [num_rows, row_len]
   float* s0;
   float* s1;
@@ -310,6 +311,9 @@ __device__ __forceinline__ void rsp_update_elem(const RspUpdate& up, int64_t o, 
     const float omb1 = __fsub_rn(1.f, up.beta1), omb2 = __fsub_rn(1.f, up.beta2);
     if (up.clip >= 0.f) {
       gr = clipf(gr, up.clip);
+      m = __fadd_rn(__fmul_rn(up.beta1, m), __fmul_rn(omb1, gr));
+      v = __fadd_rn(__fmul_rn(up.beta2, v), __fmul_rn(omb2, __fmul_rn(gr, gr)));
+    } else if (up.std_update) {   // AdamStdDnsRspDnsKernel (optimizer_op.cc:196-229): (1-beta2)*square(g')
       m = __fadd_rn(__fmul_rn(up.beta1, m), __fmul_rn(omb1, gr));
       v = __fadd_rn(__fmul_rn(up.beta2, v), __fmul_rn(omb2, __fmul_rn(gr, gr)));
     } else {
@@ -575,6 +579,50 @@ rsp_reduce2_kernel(const RspSources in, const int64_t* __restrict__ uniq, const 
 #pragma unroll
         for (int j = 0; j < W; ++j) rsp_update_elem<MODE>(up, o + j, acc[j]);
       }
+    }
+  }
+}
+
+// Standard (non-lazy) update, SGDMomStdDnsRspDnsKernel / AdamStdDnsRspDnsKernel (optimizer_op.cc:108-286,
+// optimizer_op.cu:32-223): EVERY row of this rank's shard is updated; a row that is absent from the
+// merged gradient (midx sorted unique, nnr rows, values mval) takes part with a zero gradient.
+template <int MODE, bool VEC>
+__global__ void __launch_bounds__(128)
+rsp_std_update_kernel(const int64_t* __restrict__ midx, const int64_t* __restrict__ nnr_ptr,
+                      const float* __restrict__ mval, int64_t row_len, int64_t row_lo, int64_t row_hi,
+                      const RspUpdate up) {
+  __shared__ int64_t s_pos;
+  const int64_t nnr = nnr_ptr[0];
+  constexpr int W = VEC ? 4 : 1;
+  for (int64_t row = row_lo + blockIdx.x; row < row_hi; row += gridDim.x) {
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      int64_t lo = 0, hi = nnr - 1, found = -1;
+      while (lo <= hi) {
+        const int64_t m = lo + (hi - lo) / 2;
+        const int64_t v = midx[m];
+        if (v == row) { found = m; break; }
+        if (v < row) lo = m + 1; else hi = m - 1;
+      }
+      s_pos = found;
+    }
+    __syncthreads();
+    const int64_t p = s_pos;
+    for (int64_t c = static_cast<int64_t>(threadIdx.x) * W; c < row_len; c += 128 * W) {
+      float g[W];
+#pragma unroll
+      for (int j = 0; j < W; ++j) g[j] = 0.f;
+      if (p >= 0) {
+        if constexpr (VEC) {
+          const float4 v = *reinterpret_cast<const float4*>(mval + p * row_len + c);
+          g[0] = v.x; g[1] = v.y; g[2] = v.z; g[3] = v.w;
+        } else {
+          g[0] = mval[p * row_len + c];
+        }
+      }
+      const int64_t o = (row - row_lo) * row_len + c;
+#pragma unroll
+      for (int j = 0; j < W; ++j) rsp_update_elem<MODE>(up, o + j, g[j]);
     }
   }
 }

@@ -407,6 +407,7 @@ class B200(KVStoreBase):
     # ------------------------------------------------------------------ optimizer
     def _send_optimizer(self):
         o = self._updater.optimizer if self._updater is not None else None
+        std = int(o is not None and not getattr(o, "lazy_update", True))   # optimizer.py:577-580,1595-1600
         if o is None:
             desc = (0,) * 3 + (0.0,) * 6 + (-1.0, -1.0, -1.0)
         else:
@@ -428,6 +429,7 @@ class B200(KVStoreBase):
                         o.beta1, o.beta2, o.epsilon, o.rescale_grad, clip,
                         o.lower_bound if o.lower_bound else -1.0,
                         o.upper_bound if o.upper_bound else -1.0, gclip)
+        desc = tuple(desc) + (std,)
         if desc != self._opt_sent:
             if self._handle is None:        # lazy mode: sent when the handle comes up
                 self._opt_sent = desc

@@ -213,3 +213,46 @@ def multi_sum_sq_static(arrays, out=None):
         check_call(lib.b200kv_multi_sum_sq_static(n, _dtype_flag(arrays[0]), _pp(arrays), sizes,
                                                   C.c_void_p(out.data_ptr()), stream))
     return out
+
+
+def sgd_update(weight, grad, lr, wd=0.0, rescale_grad=1.0, clip_gradient=-1.0, weight32=None):
+    """sgd_update / mp_sgd_update (optimizer_op-inl.h:382-419,656-699): single tensor, no momentum,
+    the (1 - lr*wd)*w form.  weight32 (fp32 master) selects the multi-precision op."""
+    lib = _lib.load()
+    assert weight.is_cuda and weight.is_contiguous() and grad.is_contiguous() and weight.dtype == grad.dtype
+    assert (weight.dtype == torch.float16) == (weight32 is not None), "fp16 weights need weight32, fp32 must not pass it"
+    stream = C.c_void_p(torch.cuda.current_stream(weight.device).cuda_stream)
+    with torch.cuda.device(weight.device):
+        check_call(lib.b200kv_sgd_update(_dtype_flag(weight), C.c_void_p(weight.data_ptr()), C.c_void_p(grad.data_ptr()),
+                                         C.c_void_p(weight32.data_ptr()) if weight32 is not None else None,
+                                         weight.numel(), lr, wd, rescale_grad, clip_gradient, stream))
+
+
+def lamb_update_phase1(weight, grad, mean, var, t, wd=0.0, beta1=0.9, beta2=0.999, epsilon=1e-6,
+                       bias_correction=True, rescale_grad=1.0, clip_gradient=-1.0, out=None):
+    """lamb_update_phase1 (optimizer_op-inl.h:1567-1704), fp32: updates mean / var in place, returns g."""
+    lib = _lib.load()
+    out = torch.empty_like(weight) if out is None else out
+    for x in (weight, grad, mean, var, out):
+        assert x.is_cuda and x.is_contiguous() and x.dtype == torch.float32 and x.numel() == weight.numel()
+    stream = C.c_void_p(torch.cuda.current_stream(weight.device).cuda_stream)
+    with torch.cuda.device(weight.device):
+        check_call(lib.b200kv_lamb_update_phase1(
+            C.c_void_p(out.data_ptr()), C.c_void_p(weight.data_ptr()), C.c_void_p(grad.data_ptr()),
+            C.c_void_p(mean.data_ptr()), C.c_void_p(var.data_ptr()), weight.numel(), beta1, beta2, epsilon, int(t),
+            int(bool(bias_correction)), wd, rescale_grad, clip_gradient, stream))
+    return out
+
+
+def lamb_update_phase2(weight, g, r1, r2, lr, lower_bound=-1.0, upper_bound=-1.0):
+    """lamb_update_phase2 (optimizer_op-inl.h:1706-1763), fp32, in place on weight; r1 / r2 are
+    1-element CUDA tensors (||weight||, ||g||)."""
+    lib = _lib.load()
+    for x in (weight, g):
+        assert x.is_cuda and x.is_contiguous() and x.dtype == torch.float32 and x.numel() == weight.numel()
+    assert r1.is_cuda and r2.is_cuda and r1.dtype == torch.float32 and r2.dtype == torch.float32
+    stream = C.c_void_p(torch.cuda.current_stream(weight.device).cuda_stream)
+    with torch.cuda.device(weight.device):
+        check_call(lib.b200kv_lamb_update_phase2(C.c_void_p(weight.data_ptr()), C.c_void_p(g.data_ptr()),
+                                                 C.c_void_p(r1.data_ptr()), C.c_void_p(r2.data_ptr()), weight.numel(),
+                                                 lr, lower_bound, upper_bound, stream))

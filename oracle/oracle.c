@@ -313,6 +313,66 @@ int mxref_multi_lamb(int dtype, int has_mp, int count, void** weights, void** gr
   return 0;
 }
 
+/* SGDKernel / MP_SGDKernel::Map, optimizer_op-inl.h:382-399,656-679: single tensor, no momentum.
+ * w32 != NULL: multi-precision (fp16 out, fp32 master). */
+int mxref_sgd_update(int64_t n, void* out, const void* w, const void* g, float* w32, float clip, float lr,
+                     float wd, float rescale) {
+  if (w32) {
+    const f16* g16 = (const f16*)g;
+    f16* o16 = (f16*)out;
+    for (int64_t i = 0; i < n; ++i) {
+      float x = w32[i];
+      if (clip >= 0.0f) x = (1.f - lr * wd) * x - (lr) * clipf(rescale * h2f(g16[i]), clip);
+      else x = (1.f - lr * wd) * x - (lr * rescale) * h2f(g16[i]);
+      w32[i] = x;
+      o16[i] = f2h(x);
+    }
+  } else {
+    const float* wf = (const float*)w;
+    const float* gf = (const float*)g;
+    float* of = (float*)out;
+    for (int64_t i = 0; i < n; ++i) {
+      if (clip >= 0.0f) of[i] = (1.f - lr * wd) * wf[i] - (lr) * clipf(rescale * gf[i], clip);
+      else of[i] = (1.f - lr * wd) * wf[i] - (lr * rescale) * gf[i];
+    }
+  }
+  return 0;
+}
+
+/* LambUpdatePhaseOneKernel / LambUpdatePhaseTwoKernel::Map, optimizer_op-inl.h:1622-1649,1706-1730 (fp32);
+ * beta^t = (float)pow((double)beta, t) as LambUpdatePhaseOne computes it (:1661-1662); note the
+ * double-precision division of the mean's bias correction (`1.` literal, :1643). */
+int mxref_lamb_phase1(int64_t n, float* out, float* mean, float* var, const float* w, const float* g,
+                      float clip, float rescale, float beta1, float beta2, float wd, float eps, int t,
+                      int bias_correction) {
+  const float b1t = (float)pow((double)beta1, (double)t), b2t = (float)pow((double)beta2, (double)t);
+  for (int64_t i = 0; i < n; ++i) {
+    float gr = g[i] * rescale;
+    if (clip >= 0.f) gr = clipf(gr, clip);
+    mean[i] = beta1 * mean[i] + (1.f - beta1) * gr;
+    var[i] = beta2 * var[i] + (1.f - beta2) * gr * gr;
+    float u = mean[i] / (sqrtf(var[i]) + eps) + wd * w[i];
+    if (bias_correction) {
+      float mh = (float)(mean[i] / (1. - b1t));
+      float vh = var[i] / (1 - b2t);
+      u = mh / (sqrtf(vh) + eps) + wd * w[i];
+    }
+    out[i] = u;
+  }
+  return 0;
+}
+
+int mxref_lamb_phase2(int64_t n, float* out, const float* w, const float* g, float r1, float r2, float lr,
+                      float lower, float upper) {
+  float nr1 = r1;
+  if (lower >= 0) nr1 = nr1 > lower ? nr1 : lower;
+  if (upper >= 0) nr1 = nr1 < upper ? nr1 : upper;
+  if (nr1 == 0.0f || r2 == 0.0f) lr = lr * 1.0f;
+  else lr = lr * nr1 / r2;
+  for (int64_t i = 0; i < n; ++i) out[i] = w[i] - lr * g[i];
+  return 0;
+}
+
 /* SGDMomDnsRspDnsKernel<req,cpu>::Map, optimizer_op-inl.h:747-774 — lazy update: only the rows
  * named by the gradient's indices are touched. */
 int mxref_sgd_mom_rsp(int64_t nnr, int64_t row_len, float* out, float* mom, const float* w,
@@ -341,6 +401,52 @@ int mxref_sgd_rsp(int64_t nnr, int64_t row_len, float* out, const float* w, cons
       int64_t di = idx[i] * row_len + j, gi = i * row_len + j;
       if (clip >= 0.0f) out[di] = (1.f - lr * wd) * w[di] - (lr) * clipf(rescale * g[gi], clip);
       else out[di] = (1.f - lr * wd) * w[di] - (lr * rescale) * g[gi];
+    }
+  }
+  return 0;
+}
+
+/* SGDMomStdDnsRspDnsKernel<req,cpu>::Map (optimizer_op.cc:108-140): standard update — EVERY row of the
+ * [num_rows, row_len] weight is updated, rows absent from idx with a zero gradient. */
+int mxref_sgd_mom_std_rsp(int64_t num_rows, int64_t nnr, int64_t row_len, float* out, float* mom, const float* w,
+                          const int64_t* idx, const float* g, float clip, float momentum, float lr, float wd,
+                          float rescale, int nthread) {
+  const float rate = lr * wd;
+#pragma omp parallel for num_threads(nthread)
+  for (int64_t i = 0; i < num_rows; ++i) {
+    int64_t lo = 0, hi = nnr - 1, p = -1;
+    while (lo <= hi) { int64_t m = (lo + hi) / 2; if (idx[m] == i) { p = m; break; } if (idx[m] < i) lo = m + 1; else hi = m - 1; }
+    for (int64_t j = 0; j < row_len; ++j) {
+      const int64_t di = i * row_len + j;
+      const float grad = p >= 0 ? g[p * row_len + j] : 0.f;
+      if (clip >= 0.0f) mom[di] = momentum * mom[di] - rate * w[di] - lr * clipf(rescale * grad, clip);
+      else mom[di] = momentum * mom[di] - rate * w[di] - lr * rescale * grad;
+      out[di] = w[di] + mom[di];
+    }
+  }
+  return 0;
+}
+
+/* AdamStdDnsRspDnsKernel<req,cpu>::Map (optimizer_op.cc:196-229) */
+int mxref_adam_std_rsp(int64_t num_rows, int64_t nnr, int64_t row_len, float* out, float* mean, float* var,
+                       const float* w, const int64_t* idx, const float* g, float clip, float beta1, float beta2,
+                       float lr, float wd, float eps, float rescale, int nthread) {
+#pragma omp parallel for num_threads(nthread)
+  for (int64_t i = 0; i < num_rows; ++i) {
+    int64_t lo = 0, hi = nnr - 1, p = -1;
+    while (lo <= hi) { int64_t m = (lo + hi) / 2; if (idx[m] == i) { p = m; break; } if (idx[m] < i) lo = m + 1; else hi = m - 1; }
+    for (int64_t j = 0; j < row_len; ++j) {
+      const int64_t di = i * row_len + j;
+      const float gr = p >= 0 ? (float)(g[p * row_len + j] * rescale + w[di] * wd) : (float)(w[di] * wd);
+      if (clip >= 0.0f) {
+        const float c = clipf(gr, clip);
+        mean[di] = beta1 * mean[di] + (1.f - beta1) * c;
+        var[di] = beta2 * var[di] + (1.f - beta2) * (c * c);
+      } else {
+        mean[di] = beta1 * mean[di] + (1.f - beta1) * gr;
+        var[di] = beta2 * var[di] + (1.f - beta2) * (gr * gr);
+      }
+      out[di] = w[di] - lr * mean[di] / (sqrtf(var[di]) + eps);
     }
   }
   return 0;

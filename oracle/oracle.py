@@ -75,7 +75,9 @@ class Oracle:
             else:
                 raise FileNotFoundError(path)
         self.backend = backend
-        self.lib = C.CDLL(path)
+        # lazy binding: the reference .cc files pulled into oracle/_ref name engine / storage functions
+        # that are never called on this path (and are not linked in)
+        self.lib = C.CDLL(path, mode=os.RTLD_LAZY)
         self.nthread = nthread or max(1, (os.cpu_count() or 2) // 2)  # src/engine/openmp.cc:47-53
         L = self.lib
         fp = C.c_float
@@ -90,6 +92,11 @@ class Oracle:
         L.mxref_multi_lars.argtypes = [C.c_int] + [C.c_void_p] * 5 + [fp] * 3
         L.mxref_multi_sum_sq.argtypes = [C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int]
         L.mxref_sgd_mom_rsp.argtypes = [C.c_int64, C.c_int64] + [C.c_void_p] * 5 + [fp] * 5 + [C.c_int]
+        L.mxref_sgd_mom_std_rsp.argtypes = [C.c_int64] * 3 + [C.c_void_p] * 5 + [fp] * 5 + [C.c_int]
+        L.mxref_adam_std_rsp.argtypes = [C.c_int64] * 3 + [C.c_void_p] * 6 + [fp] * 7 + [C.c_int]
+        L.mxref_sgd_update.argtypes = [C.c_int64] + [C.c_void_p] * 4 + [fp] * 4
+        L.mxref_lamb_phase1.argtypes = [C.c_int64] + [C.c_void_p] * 5 + [fp] * 6 + [C.c_int, C.c_int]
+        L.mxref_lamb_phase2.argtypes = [C.c_int64] + [C.c_void_p] * 3 + [fp] * 5
         L.mxref_sgd_rsp.argtypes = [C.c_int64, C.c_int64] + [C.c_void_p] * 4 + [fp] * 4 + [C.c_int]
         L.mxref_adam_rsp.argtypes = [C.c_int64, C.c_int64] + [C.c_void_p] * 6 + [fp] * 7 + [C.c_int]
         L.mxref_adagrad_rsp.argtypes = [C.c_int64, C.c_int64] + [C.c_void_p] * 5 + [fp] * 4 + [C.c_int]
@@ -214,6 +221,34 @@ class Oracle:
         self.lib.mxref_sgd_mom_rsp(len(idx), row_len, w.ctypes.data, mom.ctypes.data, w.ctypes.data,
                                    idx.ctypes.data, g.ctypes.data, clip, momentum, lr, wd, rescale,
                                    self.nthread)
+
+    def sgd_mom_std_rsp(self, w, mom, idx, g, lr, wd, momentum, rescale=1.0, clip=-1.0):
+        """sgd_mom_update, row-sparse grad, lazy_update=False: every row of w (optimizer_op.cc:108-140)."""
+        self.lib.mxref_sgd_mom_std_rsp(w.shape[0], len(idx), w.shape[1], w.ctypes.data, mom.ctypes.data, w.ctypes.data,
+                                       idx.ctypes.data, g.ctypes.data, clip, momentum, lr, wd, rescale, self.nthread)
+
+    def adam_std_rsp(self, w, mean, var, idx, g, lr, wd, beta1=0.9, beta2=0.999, eps=1e-8, rescale=1.0, clip=-1.0):
+        """adam_update, row-sparse grad, lazy_update=False (optimizer_op.cc:196-229)."""
+        self.lib.mxref_adam_std_rsp(w.shape[0], len(idx), w.shape[1], w.ctypes.data, mean.ctypes.data, var.ctypes.data,
+                                    w.ctypes.data, idx.ctypes.data, g.ctypes.data, clip, beta1, beta2, lr, wd, eps,
+                                    rescale, self.nthread)
+
+    def sgd_update(self, w, g, lr, wd, rescale=1.0, clip=-1.0, w32=None):
+        """sgd_update / mp_sgd_update, in place (optimizer_op-inl.h:382-399,656-679)."""
+        self.lib.mxref_sgd_update(w.size, w.ctypes.data, w.ctypes.data, g.ctypes.data,
+                                  None if w32 is None else w32.ctypes.data, clip, lr, wd, rescale)
+
+    def lamb_phase1(self, w, g, mean, var, t, wd=0.0, beta1=0.9, beta2=0.999, eps=1e-6, bias_correction=True,
+                    rescale=1.0, clip=-1.0):
+        """lamb_update_phase1 (fp32): updates mean / var in place, returns the update direction."""
+        out = np.empty_like(w)
+        self.lib.mxref_lamb_phase1(w.size, out.ctypes.data, mean.ctypes.data, var.ctypes.data, w.ctypes.data,
+                                   g.ctypes.data, clip, rescale, beta1, beta2, wd, eps, int(t), int(bias_correction))
+        return out
+
+    def lamb_phase2(self, w, g, r1, r2, lr, lower=-1.0, upper=-1.0):
+        """lamb_update_phase2 (fp32), in place on w."""
+        self.lib.mxref_lamb_phase2(w.size, w.ctypes.data, w.ctypes.data, g.ctypes.data, r1, r2, lr, lower, upper)
 
     def sgd_rsp(self, w, idx, g, lr, wd, rescale=1.0, clip=-1.0):
         """sgd_update with a row-sparse gradient, lazy rows, no momentum (optimizer_op-inl.h:452-475)."""

@@ -33,6 +33,8 @@
 // The LAMB step functors and CalcSumSq live in .cc files; pull them in as-is.
 #include "operator/contrib/multi_sum_sq.cc"
 #include "operator/contrib/multi_lamb.cc"
+// The standard (non-lazy) sparse update functors are specialised in optimizer_op.cc (:108-229).
+#include "operator/optimizer_op.cc"
 
 namespace mxnet {
 // The only engine symbol the included TUs reference but never call on our path.
@@ -255,6 +257,38 @@ int mxref_multi_sgd(int dtype, int has_mom, int has_mp, int count, void** weight
   return 0;
 }
 
+// sgd_update / mp_sgd_update: the reference's SGDKernel / MP_SGDKernel (optimizer_op-inl.h:382-399,656-679)
+int mxref_sgd_update(int64_t n, void* out, const void* w, const void* g, float* w32, float clip, float lr,
+                     float wd, float rescale) {
+  for (int64_t i = 0; i < n; ++i) {
+    if (w32)
+      MP_SGDKernel::Map<half_t>(i, static_cast<half_t*>(out), static_cast<const half_t*>(w),
+                                static_cast<const half_t*>(g), w32, clip, lr, wd, rescale, kWriteTo);
+    else
+      SGDKernel::Map<float>(i, static_cast<float*>(out), static_cast<const float*>(w),
+                            static_cast<const float*>(g), clip, lr, wd, rescale, kWriteTo);
+  }
+  return 0;
+}
+
+// lamb_update_phase1 / phase2: LambUpdatePhaseOneKernel / LambUpdatePhaseTwoKernel (optimizer_op-inl.h:1622-1730)
+int mxref_lamb_phase1(int64_t n, float* out, float* mean, float* var, const float* w, const float* g,
+                      float clip, float rescale, float beta1, float beta2, float wd, float eps, int t,
+                      int bias_correction) {
+  const float beta1_t = std::pow(beta1, t), beta2_t = std::pow(beta2, t);   // :1661-1662 (float, int -> double pow)
+  for (int64_t i = 0; i < n; ++i)
+    LambUpdatePhaseOneKernel::Map<float>(i, out, mean, var, w, g, clip, rescale, beta1, beta1_t, beta2, beta2_t,
+                                         wd, eps, t, bias_correction != 0, kWriteTo);
+  return 0;
+}
+
+int mxref_lamb_phase2(int64_t n, float* out, const float* w, const float* g, float r1, float r2, float lr,
+                      float lower, float upper) {
+  for (int64_t i = 0; i < n; ++i)
+    LambUpdatePhaseTwoKernel::Map<float>(i, out, w, g, &r1, &r2, lr, lower, upper, kWriteTo);
+  return 0;
+}
+
 int mxref_sgd_mom(int64_t n, float* out, float* mom, const float* w, const float* g, float clip,
                   float momentum, float lr, float wd, float rescale) {
   for (int64_t i = 0; i < n; ++i)
@@ -348,6 +382,37 @@ int mxref_sgd_mom_rsp(int64_t nnr, int64_t row_len, float* out, float* mom, cons
   for (int64_t i = 0; i < nnr; ++i)
     SGDMomDnsRspDnsKernel<kWriteTo, cpu>::Map<float, int64_t>(i, row_len, out, mom, w, idx, g, clip,
                                                             momentum, lr, wd, rescale);
+  return 0;
+}
+
+// standard (non-lazy) updates: the reference functors of optimizer_op.cc take the inclusive prefix sum of
+// the row flags, as SGDMomStdUpdateDnsRspDnsImpl<cpu> builds it (optimizer_op.cc:170-190)
+static std::vector<nnvm::dim_t> row_prefix(int64_t num_rows, int64_t nnr, const int64_t* idx) {
+  std::vector<nnvm::dim_t> p(num_rows, 0);
+  for (int64_t i = 0; i < nnr; ++i) p[idx[i]] = 1;
+  for (int64_t i = 1; i < num_rows; ++i) p[i] += p[i - 1];
+  return p;
+}
+
+int mxref_sgd_mom_std_rsp(int64_t num_rows, int64_t nnr, int64_t row_len, float* out, float* mom, const float* w,
+                          const int64_t* idx, const float* g, float clip, float momentum, float lr, float wd,
+                          float rescale, int nthread) {
+  const std::vector<nnvm::dim_t> p = row_prefix(num_rows, nnr, idx);
+#pragma omp parallel for num_threads(nthread)
+  for (int64_t i = 0; i < num_rows; ++i)
+    SGDMomStdDnsRspDnsKernel<kWriteTo, cpu>::Map<float, int64_t, nnvm::dim_t>(
+        static_cast<int>(i), row_len, out, mom, w, idx, g, p.data(), clip, momentum, lr, wd, rescale);
+  return 0;
+}
+
+int mxref_adam_std_rsp(int64_t num_rows, int64_t nnr, int64_t row_len, float* out, float* mean, float* var,
+                       const float* w, const int64_t* idx, const float* g, float clip, float beta1, float beta2,
+                       float lr, float wd, float eps, float rescale, int nthread) {
+  const std::vector<nnvm::dim_t> p = row_prefix(num_rows, nnr, idx);
+#pragma omp parallel for num_threads(nthread)
+  for (int64_t i = 0; i < num_rows; ++i)
+    AdamStdDnsRspDnsKernel<kWriteTo, cpu>::Map<float, int64_t, nnvm::dim_t>(
+        static_cast<int>(i), row_len, out, mean, var, w, idx, g, p.data(), clip, beta1, beta2, lr, wd, eps, rescale);
   return 0;
 }
 

@@ -49,5 +49,5 @@ def test_error_convention_without_gpu():
 
 def test_optimizer_struct_layout():
     from mxnet_maintenance_b200._lib import OptimizerDesc
-    assert C.sizeof(OptimizerDesc) == 12 * 4
+    assert C.sizeof(OptimizerDesc) == 13 * 4     # 12 fields of round 1 + std_update
     assert [f[0] for f in OptimizerDesc._fields_][:4] == ["kind", "multi_precision", "bias_correction", "momentum"]

@@ -130,6 +130,10 @@ def test_row_sparse_kernels(oracle, oracle_ref):
         hh = np.zeros_like(W)
         o.adagrad_rsp(ww, hh, idx, gg, 0.1)
         o.adagrad_rsp(ww, hh, idx, gg, 0.1, rescale=0.5, clip=0.2)
+        o.sgd_mom_std_rsp(ww, mm, idx, gg, 0.1, 1e-3, 0.9)      # lazy_update=False: every row
+        o.sgd_mom_std_rsp(ww, mm, idx, gg, 0.1, 1e-3, 0.9, 0.5, 0.1)
+        o.adam_std_rsp(ww, me, va, idx, gg, 1e-3, 0.01)
+        o.adam_std_rsp(ww, me, va, idx, gg, 1e-3, 0.01, clip=0.2)
         o.sgd_rsp(ww, idx, gg, 0.1, 1e-3)                       # SGDDnsRspKernel: (1 - lr*wd)*w form
         o.sgd_rsp(ww, idx, gg, 0.1, 1e-3, 0.5, 0.1)
         return np.concatenate([ww.ravel(), mm.ravel(), me.ravel(), va.ravel(), hh.ravel()])
@@ -158,5 +162,33 @@ def test_multi_adamw(oracle, oracle_ref, mp, clip):
             o.multi_adamw(ww, g, me, va, w32, [1e-3, 2e-3, 5e-4], [0.01, 0, 0.1], [1.0, 0.5, 2.0],
                           rescale=[0.5, 0.25, float("nan"), 0.5][t], clip=clip)
         return np.concatenate([x.astype(np.float32) for x in ww] + me + va)
+    a, b = _both(oracle, oracle_ref, f)
+    assert a.tobytes() == b.tobytes()
+
+
+def test_single_tensor_sgd_and_lamb_phases(oracle, oracle_ref):
+    """sgd_update / mp_sgd_update and lamb_update_phase1/2 restatements vs the reference functors."""
+    rng = np.random.default_rng(8)
+    n = 10007
+    w0 = rng.uniform(-1, 1, n).astype(np.float32)
+    g0 = (rng.uniform(-1, 1, n) * 1e-2).astype(np.float32)
+
+    def f(o):
+        w = w0.copy()
+        o.sgd_update(w, g0, 0.1, 1e-3)
+        o.sgd_update(w, g0, 0.1, 1e-3, 0.5, 0.004)
+        w16, g16, w32 = w0.astype(np.float16), g0.astype(np.float16), w0.astype(np.float16).astype(np.float32)
+        o.sgd_update(w16, g16, 0.1, 1e-3, 0.5, -1.0, w32)
+        o.sgd_update(w16, g16, 0.1, 1e-3, 0.5, 0.004, w32)
+        wl, m, v = w0.copy(), np.zeros(n, np.float32), np.zeros(n, np.float32)
+        outs = []
+        for t in (1, 2, 7):
+            for bc in (True, False):
+                u = o.lamb_phase1(wl, g0, m, v, t, wd=0.01, bias_correction=bc, rescale=0.5, clip=0.004 if t == 2 else -1.0)
+                r1 = float(np.sqrt(np.float32((wl.astype(np.float64) ** 2).sum())))
+                r2 = float(np.sqrt(np.float32((u.astype(np.float64) ** 2).sum())))
+                o.lamb_phase2(wl, u, r1, r2, 1e-3, lower=0.5 if t == 7 else -1.0, upper=10.0 if t == 7 else -1.0)
+                outs.append(u)
+        return np.concatenate([w, w16.astype(np.float32), w32, wl, m, v] + outs)
     a, b = _both(oracle, oracle_ref, f)
     assert a.tobytes() == b.tobytes()

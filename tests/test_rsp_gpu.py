@@ -225,3 +225,35 @@ def test_row_sparse_pull_async(oracle):
     assert n == len(uniq)
     assert out.indices[:n].cpu().numpy().tobytes() == uniq.tobytes()
     assert out.data[:n].cpu().numpy().tobytes() == table[uniq].tobytes()
+
+
+@pytest.mark.parametrize("kind", ["sgd", "sgd_clip", "adam", "adam_clip"])
+@pytest.mark.parametrize("ncopies", [1, 3])
+def test_standard_row_update(oracle, kind, ncopies):
+    """lazy_update=False: EVERY row of the table is updated, rows absent from the merged gradient with a
+    zero gradient (SGDMomStdDnsRspDnsKernel / AdamStdDnsRspDnsKernel, optimizer_op.cc:108-286)."""
+    import mxnet_maintenance_b200 as mb0
+    from oracle.oracle import adam_lr
+    rng = np.random.default_rng(21)
+    num_rows, row_len = 777, 24
+    table = rng.uniform(-1, 1, (num_rows, row_len)).astype(np.float32)
+    clip = 0.004 if "clip" in kind else None
+    if kind.startswith("sgd"):
+        opt = mb0.optimizer.SGD(learning_rate=0.1, momentum=0.9, wd=1e-3, rescale_grad=0.5, clip_gradient=clip,
+                                lazy_update=False)
+    else:
+        opt = mb0.optimizer.Adam(learning_rate=1e-3, wd=0.01, rescale_grad=0.5, clip_gradient=clip, lazy_update=False)
+    kv, mb = _kv(table, opt)
+    ref = table.copy()
+    s0, s1 = np.zeros_like(ref), np.zeros_like(ref)
+    for step in range(3):
+        grads = _grads(rng, num_rows, row_len, ncopies, 60)
+        _push(kv, mb, grads)
+        midx, mval = oracle.rsp_sum(grads)
+        if kind.startswith("sgd"):
+            oracle.sgd_mom_std_rsp(ref, s0, midx, mval, 0.1, 1e-3, 0.9, 0.5, clip if clip else -1.0)
+        else:
+            oracle.adam_std_rsp(ref, s0, s1, midx, mval, adam_lr(1e-3, 0.9, 0.999, step + 1), 0.01, rescale=0.5,
+                                clip=clip if clip else -1.0)
+    pi, pv = _pull(kv, mb, torch.arange(num_rows, device="cuda"))
+    assert pv.tobytes() == ref.tobytes()

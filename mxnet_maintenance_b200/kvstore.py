@@ -266,6 +266,15 @@ class B200(KVStoreBase):
         self.auto_batch = os.environ.get("B200KV_AUTO_BATCH", "0") == "1"
         self._pending = []
         self._auto_steps = {}
+        # auto_buckets > 1: the keys of a step are split into that many buckets (in the order they were
+        # first pushed, balanced by size); a bucket is launched as soon as its last key has been
+        # pushed, so the GPU works on early buckets while the caller is still handing over the rest
+        # (the reference's priority = -index asks for exactly this order, trainer.py:392-395)
+        self.auto_buckets = int(os.environ.get("B200KV_AUTO_BUCKETS", "1"))
+        self._bucket_of = None          # key -> bucket, fixed after the first complete step
+        self._bucket_size = []
+        self._custom_updater = None     # _set_updater
+        self._reducer = None
         if self._handle is not None:
             self._bind_stream()
         if world_size > 1:
@@ -491,6 +500,8 @@ class B200(KVStoreBase):
         self._note(vals)
         if vals and _is_rsp(vals[0]):
             return self._push_rsp(keys, vals, use_str, priority)
+        if self._custom_updater is not None:
+            return self._push_custom(keys, vals)
         ck = self._keys(keys, use_str)
         self._bind_stream()
         self._before_update(keys)
@@ -520,6 +531,26 @@ class B200(KVStoreBase):
         if not self._pending:
             return
         pend, self._pending = self._pending, []
+        if self._bucket_of is None and self.auto_buckets > 1 and len(pend) == len(set(self._dense_keys)):
+            self._plan_buckets([e[0] for e in pend])
+        self._run_pending(pend)
+
+    def _plan_buckets(self, keys):
+        """Contiguous buckets over the push order of the first complete step, balanced by elements."""
+        total = float(sum(self._sizes[k] for k in keys)) or 1.0
+        nb = max(1, min(self.auto_buckets, len(keys)))
+        self._bucket_of, acc, b = {}, 0.0, 0
+        for k in keys:
+            self._bucket_of[k] = b
+            acc += self._sizes[k]
+            if acc >= total * (b + 1) / nb and b < nb - 1:
+                b += 1
+        self._bucket_size = [sum(1 for k in keys if self._bucket_of[k] == i) for i in range(nb)]
+
+    def _run_pending(self, pend):
+        # higher priority first (the reference's engine runs higher-priority pushes first)
+        pend = sorted(pend, key=lambda e: -e[3]) if len(set(e[3] for e in pend)) > 1 else pend
+        pend = [(k, v, o) for k, v, o, _ in pend]
         keys = [k for k, _, _ in pend]
         vals = [v for _, v, _ in pend]
         outs = [(o if o is not None else v) for _, v, o in pend]
@@ -533,9 +564,10 @@ class B200(KVStoreBase):
         if hit is not None and hit[1] == ptrs:
             hit[0]()
             return
-        for old in self._auto_steps.values():
-            old[0].release()
-        self._auto_steps.clear()
+        if len(self._auto_steps) >= max(4, 2 * self.auto_buckets):   # stale bound steps (arrays were replaced)
+            for old in self._auto_steps.values():
+                old[0].release()
+            self._auto_steps.clear()
         auto, self.auto_batch = self.auto_batch, False
         try:
             step = self.bind_pushpull(keys, vals, out=outs)     # runs the first replay itself
@@ -552,13 +584,28 @@ class B200(KVStoreBase):
             self._h
         if self.auto_batch and isinstance(key, (int, str)) and key in self._sizes \
                 and not _is_rsp(value if _is_array(value) else value[0]):
-            if any(k == key for k, _, _ in self._pending):
-                self.flush()
-            self._pending.append((key, value, out))
-            if len(self._pending) == len(set(self._dense_keys)):
-                self.flush()
-            return
+            if self._custom_updater is not None:
+                pass        # falls through to the immediate path below
+            else:
+                if any(e[0] == key for e in self._pending):
+                    self.flush()
+                self._pending.append((key, value, out, priority))
+                if self._bucket_of is not None and key in self._bucket_of:
+                    b = self._bucket_of[key]
+                    mine = [e for e in self._pending if self._bucket_of.get(e[0]) == b]
+                    if len(mine) == self._bucket_size[b]:        # the bucket is complete: launch it now
+                        self._pending = [e for e in self._pending if self._bucket_of.get(e[0]) != b]
+                        self._run_pending(mine)
+                elif len(self._pending) == len(set(self._dense_keys)):
+                    self.flush()
+                return
         self.flush()
+        if self._custom_updater is not None:
+            vkeys, vals, use_str = _flatten(key, value)
+            self._push_custom(vkeys, vals)
+            if out is None:
+                out = value
+            return self.pull(key, out=out, priority=priority)
         vkeys, vals, use_str = _flatten(key, value)
         if out is None:
             okeys, outs = vkeys, vals
@@ -785,8 +832,40 @@ class B200(KVStoreBase):
         self._send_optimizer()
 
     def _set_updater(self, updater):
-        raise NotImplementedError("custom Python updaters are not supported: the b200 store runs "
-                                  "its own fused CUDA updates (set_optimizer) or none")
+        """kvstore.py:692-736 / MXKVStoreSetUpdaterEx (include/mxnet/c_api.h:2985-3027): a custom Python
+        updater ``updater(key, merged, stored)`` that changes ``stored`` in place.  The reduce stays on
+        the GPU (a second, optimizer-less store merges the pushed copies in CommCPU order); the callback
+        then runs synchronously inside ``push`` on zero-copy views of the merged and the stored value,
+        like KVStoreLocal::PushImpl does (src/kvstore/kvstore_local.h:259-267).  With several GPUs the
+        callback runs once per device copy of the stored value, so it must be deterministic (the
+        reference runs it once and broadcasts).  ``None`` removes it."""
+        self.flush()
+        self._custom_updater = updater
+        if updater is not None:
+            self._updater = None
+            self._send_optimizer()
+
+    def _push_custom(self, keys, vals):
+        if self._reducer is None:
+            if self._world > 1:
+                self._reducer = B200(device_id=self._device, rank=self._rank, world_size=self._world)
+            else:
+                self._reducer = B200(devices=self.devices)
+        r = self._reducer
+        fresh = [k for k in dict.fromkeys(keys) if k not in r._sizes]
+        if fresh:
+            first = {}
+            for k, v in zip(keys, vals):
+                first.setdefault(k, v)
+            r.init(fresh, [_clone(first[k]) for k in fresh])
+        r.push(keys, vals)                              # no optimizer there: the merged value is stored
+        nmem = len(self.devices) if self._members else 1
+        for k in dict.fromkeys(keys):
+            shape = self._shapes[k]
+            for m in range(nmem):
+                merged = r.weight_view(k, shape, member=m)
+                stored = self.weight_view(k, shape, member=m)
+                self._custom_updater(k, merged, stored)
 
     def set_gradient_compression(self, compression_params):
         """2-bit compression is lossy and useless on NVLink; refused like KVStoreNCCL does

@@ -108,8 +108,6 @@ def test_errors_follow_the_reference():
         kv.push(3, torch.ones(SHAPE))             # CPU tensor: no CPU path
     with pytest.raises(m.B200KVError, match="compression"):
         kv.set_gradient_compression({"type": "2bit"})
-    with pytest.raises(NotImplementedError):
-        kv._set_updater(lambda k, g, w: None)
     kvs = init_kv(True)
     with pytest.raises(m.B200KVError, match="has not been initialized"):
         kvs.pull("zzz", out=zeros())
@@ -271,3 +269,87 @@ def test_handle_cache_does_not_pin_temporaries():
     kv.wait()
     gc.collect()
     assert torch.cuda.memory_allocated() - base < (40 << 20)
+
+
+@pytest.mark.parametrize("str_keys", [False, True])
+def test_custom_updater(str_keys):
+    """test_kvstore.py:226-280 (test_updater): ``kv._set_updater(lambda key, recv, local: local += recv)``;
+    every push of ones from 4 device copies adds 4 to the stored value (kvstore_local.h:259-267)."""
+    kv = init_kv(str_keys)
+    key, keys = ("a", STR_KEYS) if str_keys else (3, KEYS)
+    seen = []
+
+    def updater(k, recv, local):
+        seen.append(k)
+        local += recv
+    kv._set_updater(updater)
+    ndev = 4
+    vals = [ones() for _ in range(ndev)]
+    outs = [torch.empty(SHAPE, device="cuda") for _ in range(ndev)]
+    kv.push(key, vals)
+    kv.pull(key, out=outs)
+    assert all((o == ndev).all() for o in outs) and seen == [key]
+    for i in range(1, 4):                                   # accumulates over pushes
+        kv.push(keys, [[ones() for _ in range(ndev)] for _ in keys])
+        got = [[torch.empty(SHAPE, device="cuda") for _ in range(ndev)] for _ in keys]
+        kv.pull(keys, out=got)
+        assert all((o == ndev * i).all() for row in got for o in row)
+    out = torch.empty(SHAPE, device="cuda")
+    kv.pushpull(key, [ones(2), ones(3)], out=out)           # pushpull runs the updater too
+    assert (out == ndev + 5).all()
+
+
+def test_custom_updater_on_a_group():
+    """The same updater over a store that drives several (virtual) devices: the reduce is the fused
+    peer-memory exchange, the callback runs on every device copy of the stored value."""
+    m = mb()
+    kv = m.B200(devices=[0, 0])
+    w = [torch.zeros(SHAPE, device="cuda") for _ in range(2)]
+    kv.broadcast(7, w[0], out=w)
+
+    def nightly_test_optimizer(k, recv, local):             # tests/nightly/test_kvstore.py:80-99: w += rescale * g
+        local += 0.5 * recv
+    kv._set_updater(nightly_test_optimizer)
+    for i in range(1, 4):
+        kv.pushpull(7, [ones(), ones(3)], out=w)
+        kv.wait()
+        assert all((c == 2.0 * i).all() for c in w)
+
+
+def test_priority_buckets_launch_early():
+    """trainer.py:392-395 pushes parameter i with priority -i.  With auto_batch and auto_buckets = 3
+    a bucket is launched the moment its last key has been handed over — before the remaining keys
+    arrive — and the results equal the unbucketed run bit for bit."""
+    m = mb()
+    from mxnet_maintenance_b200 import shapes
+    shp = shapes.mlp() + [(33,), (4097,), (70000,)]
+    rng = np.random.default_rng(4)
+    w0 = [rng.uniform(-1, 1, s).astype(np.float32) for s in shp]
+    gs = [[(rng.uniform(-1, 1, s) * 1e-2).astype(np.float32) for s in shp] for _ in range(3)]
+    res = []
+    for buckets in (1, 3):
+        kv = m.create("b200")
+        kv.auto_batch, kv.auto_buckets = True, buckets
+        kv.set_optimizer(m.optimizer.SGD(learning_rate=0.1, momentum=0.9, wd=1e-4))
+        w = [torch.from_numpy(x).cuda() for x in w0]
+        g = [torch.empty_like(x) for x in w]
+        for i, x in enumerate(w):
+            kv.broadcast(i, x, out=[x])
+        kv.wait()
+        early = []
+        for it in range(3):
+            for d, h in zip(g, gs[it]):
+                d.copy_(torch.from_numpy(h))
+            base = kv.launch_count()
+            for i in range(len(w)):
+                kv.pushpull(i, [g[i]], out=[w[i]], priority=-i)
+                if i == len(w) - 2:
+                    early.append(kv.launch_count() - base)      # launches before the LAST key was pushed
+            kv.wait()
+        res.append([x.cpu().numpy() for x in w])
+        if buckets == 1:
+            assert early == [0, 0, 0]
+        else:
+            assert early[0] == 0 and early[1] >= 1 and early[2] >= 1   # buckets are known from step 2 on
+    for a, b in zip(*res):
+        assert a.tobytes() == b.tobytes()

@@ -70,6 +70,8 @@ def parse():
                     help="only the headline workload, no `configs` block for the other BASELINE configurations")
     ap.add_argument("--configs-budget", type=float, default=240.0,
                     help="seconds the extra configurations may take before the line is printed without them")
+    ap.add_argument("--single-process", action="store_true",
+                    help="ONE process driving --gpus N devices (b200kv_create_group), launched without torchrun")
     ap.add_argument("--no-views", action="store_true",
                     help="use caller-owned gradient/weight arrays (adds the pack / unpack / out copies) "
                          "instead of zero-copy views into the store")
@@ -80,7 +82,7 @@ def parse_args_for_check(world):
     """Argument set tests/multi_gpu_check.py uses to drive run_dense / run_rsp for their pre-flight."""
     return argparse.Namespace(gpus=world, steps=3, warmup=3, workload="resnet50", impl="b200", e2e_steps=2,
                               cpu_steps=0, no_cpu_baseline=True, no_parity=False, parity_steps=2,
-                              no_configs=True, configs_budget=240.0, no_views=False)
+                              no_configs=True, configs_budget=240.0, no_views=False, single_process=False)
 
 
 def peaks():
@@ -876,6 +878,123 @@ def run_dense(args, env, workload, steps, e2e_steps, cpu_baseline, psteps):
     return line
 
 
+def run_group(args):
+    """--single-process: ONE process drives --gpus N devices through b200kv_create_group, the reference's
+    own usage model for kvstore 'device' / 'nccl' (one array per device in every pushpull list).  Same
+    step, same metric; with fewer than N visible GPUs the members become virtual ranks on GPU 0."""
+    import torch
+    import mxnet_maintenance_b200 as mb
+    from mxnet_maintenance_b200 import shapes
+    from oracle.oracle import Oracle, have_ref
+    n = max(args.gpus, 2)
+    real = torch.cuda.device_count() >= n
+    devs = list(range(n)) if real else [0] * n
+    shp_name, dt, kind, bpe, desc = WORKLOADS[args.workload]
+    assert kind == "sgd" and dt == "f32", "--single-process measures the fp32 SGD workloads (resnet50, mlp)"
+    shp = shapes.CONFIGS[shp_name]()
+    sizes = [shapes.numel(s) for s in shp]
+    nelem = sum(sizes)
+    keys = list(range(len(shp)))
+    kw = opt_kwargs(kind, False)
+    kv = mb.B200(devices=devs)
+    kv.set_optimizer(mb.optimizer.SGD(**kw))
+    g0 = torch.Generator(device="cuda:0").manual_seed(99)
+    w_init = [(torch.rand(s, device="cuda:0", generator=g0) * 2 - 1) for s in shp]
+    kv.init(keys, w_init)
+    wv = [[kv.weight_view(k, s, member=m) for m in range(n)] for k, s in zip(keys, shp)]
+    gv = [[kv.grad_view(k, s, member=m) for m in range(n)] for k, s in zip(keys, shp)]
+    step = kv.bind_pushpull(keys, gv, out=wv)
+    gens = [torch.Generator(device="cuda:%d" % d).manual_seed(1234 + m) for m, d in enumerate(devs)]
+
+    def fresh_grads():
+        host = []
+        for m in range(n):
+            per = []
+            for k, s in zip(keys, shp):
+                g = (torch.rand(s, device=gv[k][m].device, generator=gens[m]) * 2 - 1) * 1e-2
+                gv[k][m].copy_(g)
+                per.append(g.reshape(-1).cpu().numpy())
+            host.append(per)
+        return host
+
+    def sync_all():
+        for d in sorted(set(devs)):
+            torch.cuda.synchronize(d)
+    # parity pre-flight: CommCPU reduce over the members' gradients in member order + MultiSGDKernel
+    st = ErrStat(*TOL32)
+    o = Oracle("ref" if have_ref() else "port", nthread=os.cpu_count() or 1)
+    w = [x.reshape(-1).cpu().numpy().copy() for x in w_init]
+    mom = [np.zeros(z, np.float32) for z in sizes]
+    same = True
+    for _ in range(0 if args.no_parity else args.parity_steps):
+        hg = fresh_grads()
+        sync_all()
+        step()
+        kv.wait()
+        sync_all()
+        merged = [o.reduce_sum([hg[m][k].copy() for m in range(n)]) for k in keys]
+        o.multi_sgd(w, merged, mom, None, [kw["learning_rate"]] * len(keys), [kw["wd"]] * len(keys), kw["momentum"],
+                    kw["rescale_grad"], -1.0)
+        for k in keys:
+            got = [wv[k][m].reshape(-1).cpu().numpy() for m in range(n)]
+            same = same and all(x.tobytes() == got[0].tobytes() for x in got)
+            st.add(got[0], w[k])
+    if not args.no_parity:
+        for k in keys:
+            st.add(kv.get_state(k, 0).reshape(-1), mom[k])
+    fresh_grads()
+    sync_all()
+    warmup = max(args.warmup, 3)
+    for _ in range(warmup):
+        step()
+    kv.wait()
+    sync_all()
+    clocks = Clocks(0)
+    l0 = kv.launch_count()
+    kv.set_profiling(True)
+    kv.profile_read()
+    clocks.active = True
+    t0 = time.perf_counter()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record(torch.cuda.current_stream(devs[0]))
+    for _ in range(args.steps):
+        step()
+    e1.record(torch.cuda.current_stream(devs[0]))
+    kv.wait()
+    sync_all()
+    wall_ms = (time.perf_counter() - t0) * 1e3
+    clocks.active = False
+    # device time on member 0's stream; the members finish together (in-kernel barriers), and the wall
+    # clock around the whole loop is reported beside it
+    ms = max(e0.elapsed_time(e1), 0.0)
+    kernel_ms, kernel_n = kv.profile_read()
+    launches = kv.launch_count() - l0
+    ms_step = ms / args.steps
+    sbytes = float(nelem) * 4
+    link = 2.0 * sbytes * (n - 1) / n
+    k_ms = kernel_ms / max(kernel_n, 1)
+    par = dict(st.result(), checked=not args.no_parity, steps=args.parity_steps, exchange=kv.last_exchange(),
+               all_ranks_bit_identical_weights=same)
+    par["pass"] = par["pass"] and same
+    line = {"metric": "grad-sync+update steps/s", "value": 1e3 / ms_step, "unit": "steps/s", "n_gpus": n,
+            "steps": args.steps, "warmup": warmup, "ms_per_step": ms_step, "wall_ms_per_step": wall_ms / args.steps,
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": dt, "data": "synthetic",
+            "config": config_of(args.workload, n),
+            "setup": {"parallelism": "ONE process driving %d %s through b200kv_create_group (peer memory, no NCCL)"
+                                     % (n, "GPUs" if real else "virtual ranks on GPU 0"),
+                      "arrays": "zero-copy views into the store, one per device", "exchange": kv.last_exchange()},
+            "roofline": {"bound": "nvlink" if real else "hbm", "achieved": link / (k_ms * 1e-3) / 1e9, "peak": 770.0,
+                         "unit": "GB/s", "frac": link / (k_ms * 1e-3) / 1e9 / 770.0, "traffic": None,
+                         "kernel": "mta_kernel over peer memory: fused reduce-scatter + sgd update + all-gather "
+                                   "(one launch per device per step)",
+                         "link_bytes_per_direction_per_step": link, "kernel_ms_per_step": k_ms,
+                         "launches_per_step": launches / args.steps},
+            "e2e": {"value": None, "unit": "steps/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0,
+                    "what": "not measured in this mode"},
+            "parity": par, "gpu_launches": launches, "clocks": clocks.snapshot()}
+    print(json.dumps(line), flush=True)
+
+
 def run_b200(args):
     env = Env(args)
     rank, world = env.rank, env.world
@@ -931,5 +1050,7 @@ if __name__ == "__main__":
     a = parse()
     if a.impl == "reference":
         run_reference(a)
+    elif a.single_process:
+        run_group(a)
     else:
         run_b200(a)

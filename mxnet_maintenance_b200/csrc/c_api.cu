@@ -44,14 +44,22 @@ static Group* G(b200kv_handle h) {
   KV_CHECK(b->is_group, "this entry point needs a handle made by b200kv_create_group");
   return static_cast<Group*>(b);
 }
+// a group works on several devices in turn: the caller's current device is put back afterwards
+struct KeepDevice {
+  int d = -1;
+  explicit KeepDevice(bool on) { if (on) cudaGetDevice(&d); }
+  ~KeepDevice() { if (d >= 0) cudaSetDevice(d); }
+};
 // the same call on whichever object the handle is
 #define KV(h, call)                                      \
   do {                                                   \
+    KeepDevice keep_(H(h)->is_group);                    \
     if (H(h)->is_group) static_cast<Group*>(H(h))->call; \
     else static_cast<Store*>(H(h))->call;                \
   } while (0)
 #define KVR(h, lhs, call)                                      \
   do {                                                         \
+    KeepDevice keep_(H(h)->is_group);                          \
     if (H(h)->is_group) lhs = static_cast<Group*>(H(h))->call; \
     else lhs = static_cast<Store*>(H(h))->call;                \
   } while (0)
@@ -75,6 +83,7 @@ int b200kv_create(int device_id, int rank, int world_size, b200kv_handle* out) {
 int b200kv_create_group(int ndev, const int* dev_ids, b200kv_handle* out) {
   API_BEGIN();
   KV_CHECK(dev_ids != nullptr && out != nullptr, "null argument");
+  KeepDevice keep_(true);
   *out = static_cast<KVHandle*>(new Group(ndev, dev_ids));
   API_END();
 }
@@ -87,6 +96,7 @@ int b200kv_group_set_streams(b200kv_handle h, int n, void* const* streams) {
 
 int b200kv_group_view(b200kv_handle h, int member, int key, int which, DLManagedTensor** out) {
   API_BEGIN();
+  KeepDevice keep_(true);
   *out = G(h)->view(member, key, which);
   API_END();
 }
@@ -239,6 +249,7 @@ int b200kv_last_global_norm(b200kv_handle h, float* out) {
 
 int b200kv_view(b200kv_handle h, int key, int which, DLManagedTensor** out) {
   API_BEGIN();
+  KeepDevice keep_(H(h)->is_group);
   *out = H(h)->is_group ? G(h)->view(0, key, which) : S(h)->view(key, which);
   API_END();
 }

@@ -5,7 +5,7 @@ for f in sys.argv[1:]:
     d = json.loads(open(f).read().strip().splitlines()[-1])
     r, par = d["roofline"], d.get("parity") or {}
     print(f, "N", d.get("n_gpus"), "value", round(d["value"], 1), "ms", round(d["ms_per_step"], 4), "frac", round(r["frac"], 3),
-          "kms", round(r.get("kernel_ms_per_step") or 0, 4), "e2e", round(d["e2e"]["value"], 1), "parity", par.get("pass"),
+          "kms", round(r.get("kernel_ms_per_step") or 0, 4), "e2e", round(d["e2e"]["value"] or 0, 1), "parity", par.get("pass"),
           par.get("bit_exact"), par.get("exchange"))
     for n, c in d.get("configs", {}).items():
         if isinstance(c, dict) and "value" in c:

@@ -472,7 +472,7 @@ def run_rsp(args, env, steps, e2e_steps, cpu_baseline):
                     st.max_over_tol = float("inf")
         if rank == 0:
             parity = dict(st.result(), checked=True, steps=psteps, indices_bit_exact=idx_ok,
-                          exchange="local" if world == 1 else "owner-sharded table: owners read their row range from the senders over NVLink",
+                          exchange="local" if world == 1 else "owner-sharded table (row id % ranks): owners read their rows from the senders over NVLink",
                           oracle="ElementwiseSumRsp restatement (ndarray_function.cc:59-176) + reference "
                                  "SGDMomDnsRspDnsKernel + UniqueImpl<cpu>; rank 0's pulled rows compared")
             parity["pass"] = parity["pass"] and idx_ok

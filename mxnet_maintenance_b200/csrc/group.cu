@@ -373,7 +373,7 @@ void Group::push_rsp(int key, int ncopies, DLManagedTensor* const* idx, DLManage
   if (size() == 1) return m_[0]->push_rsp(key, ncopies, idx, val);
   // CommDevice::ReduceRowSparse (comm.h:478-501) gathers every copy on one device; here every member
   // reads ALL copies in list order (= the reference's device order), its siblings' through peer
-  // memory.  With an optimizer each member reduces and updates only the rows it owns (range-partitioned
+  // memory.  With an optimizer each member reduces and updates only the rows it owns (dealt cyclically (row id % members)
   // table and state); without one every member stores the identical merged value
   fence_in(true);
   for (auto& m : m_) {
@@ -381,7 +381,7 @@ void Group::push_rsp(int key, int ncopies, DLManagedTensor* const* idx, DLManage
     m->push_rsp(key, ncopies, idx, val);
   }
   if (m_[0]->rsp_is_sharded(key)) {
-    // with an optimizer the table and its state are range-partitioned over the members (each one
+    // with an optimizer the table and its state are dealt cyclically (row id % members) over the members (each one
     // reduced and updated only the rows it owns); pulls gather from every member's shard
     const float* tabs[kMaxCopies] = {nullptr};
     for (int i = 0; i < size(); ++i) tabs[i] = m_[i]->rsp_table_ptr(key);

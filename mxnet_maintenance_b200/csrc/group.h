@@ -47,7 +47,7 @@ class Group : public KVHandle {
   int64_t launches() const;
   const char* last_exchange() const { return m_[0]->last_exchange(); }
   // row sparse: every member reads all copies (its siblings' through peer memory); with an optimizer
-  // the table is range-partitioned over the members, each reducing / updating the rows it owns
+  // the table is dealt cyclically (row id % members) over the members, each reducing / updating the rows it owns
   void init_rsp(int key, DLManagedTensor* dense_value);
   void push_rsp(int key, int ncopies, DLManagedTensor* const* idx, DLManagedTensor* const* val);
   int64_t rsp_merged_size(int key);

@@ -20,8 +20,9 @@ struct RspKey {
   int key = 0;
   int64_t num_rows = 0, row_len = 0;
   int bits = 0;             // significant bits of a row id
-  // rows [row_lo, row_hi) of the table live on this rank (everything unless the key is sharded)
-  int64_t row_lo = 0, row_hi = 0, rows_per_rank = 0;
+  // this rank holds the rows row_lo + j*stride, j in [0, nlocal): everything (0, 1, num_rows) unless the
+  // key is sharded — then the rows with id % world == rank (rows_per_rank = ceil(num_rows / world))
+  int64_t row_lo = 0, stride = 1, nlocal = 0, rows_per_rank = 0;
   DevBuf table, s0, s1;     // dense [num_rows, row_len] value and optimizer state
   bool has_s0 = false, has_s1 = false;
   bool full = true;         // the table holds every row; false: compact (c_idx, c_val) holds the value
@@ -67,7 +68,7 @@ struct RspKey {
   bool merged_valid = false;
   // multi-rank exchange buffers: this rank's rows packed contiguously, and every rank's rows
   DevBuf send_idx, send_val, recv_idx, recv_val, counts_dev;
-  // Owner-sharded layout (several ranks + an optimizer): rank r keeps rows [r*rows_per_rank, ...) of
+  // Owner-sharded layout (several ranks + an optimizer): rank r keeps the rows with id % world == r of
   // the table and of the optimizer state only; peer_table[o] is rank o's shard as seen from here
   bool sharded = false;
   const float* peer_table[kMaxCopies] = {nullptr};
@@ -156,11 +157,12 @@ void unique_heads(RspKey& k, const uint32_t* keys, int n, cudaStream_t st, int64
 
 namespace {
 
-// sorted unique ids of the marked rows in [row_lo, row_hi) -> k.uniq / k.count[0]; clears the bitmap
-void compact_bitmap(RspKey& k, int64_t row_lo, int64_t row_hi, cudaStream_t st, int64_t* launches) {
-  const int nw = static_cast<int>((row_hi - row_lo + 31) / 32);
+// sorted unique ids of the marked rows (ids row_lo + j*stride, j < nlocal) -> k.uniq / k.count[0]; clears
+// the bitmap
+void compact_bitmap(RspKey& k, int64_t row_lo, int64_t stride, int64_t nlocal, cudaStream_t st, int64_t* launches) {
+  const int nw = static_cast<int>((nlocal + 31) / 32);
   const int ncta = std::max(1, (nw + kCompactWords - 1) / kCompactWords);
-  rsp_compact_kernel<<<ncta, 256, 0, st>>>(k.bitmap.as<uint32_t>(), ncta * kCompactWords, row_lo,
+  rsp_compact_kernel<<<ncta, 256, 0, st>>>(k.bitmap.as<uint32_t>(), ncta * kCompactWords, row_lo, stride,
                                            k.uniq.as<int64_t>(), k.count.as<int64_t>(),
                                            k.chain.as<uint32_t>(), ++k.scan_epoch);
   CUDA_OK(cudaGetLastError());
@@ -169,11 +171,11 @@ void compact_bitmap(RspKey& k, int64_t row_lo, int64_t row_hi, cudaStream_t st, 
 
 template <int MODE>
 void launch_reduce2(bool vec, bool direct, int grid, cudaStream_t st, const RspSources& src, RspKey& k,
-                    int64_t row_lo, int64_t row_hi, float* out_val, int64_t* out_idx, int64_t* out_nnr,
+                    int64_t row_lo, int64_t stride, float* out_val, int64_t* out_idx, int64_t* out_nnr,
                     const RspUpdate& up) {
 #define GO(V, D)                                                                                        \
   rsp_reduce2_kernel<MODE, V, D><<<grid, 128, 0, st>>>(src, k.uniq.as<int64_t>(), k.count.as<int64_t>(), \
-                                                       k.row_len, k.num_rows, row_lo, row_hi, out_val,  \
+                                                       k.row_len, k.num_rows, row_lo, stride, out_val,  \
                                                        out_idx, out_nnr, up, k.err())
   if (vec && direct) GO(true, true);
   else if (vec) GO(true, false);
@@ -186,22 +188,26 @@ void launch_reduce2(bool vec, bool direct, int grid, cudaStream_t st, const RspS
 }  // namespace
 
 // ---- owner-sharded layout ---------------------------------------------------------------------------------
-// With several ranks and an optimizer every rank keeps only rows [rank*rows_per_rank, ...) of the table
-// and of the optimizer state (owner = row_id / rows_per_rank).  The full table the key was
-// initialised with is cut down at the first such push.
+// With several ranks and an optimizer every rank keeps only the rows with id % world == rank of the table
+// and of the optimizer state.  SURVEY §8(e) proposed owner = row_id / rows_per_rank; embedding ids are
+// heavily skewed towards small ids (Zipf), which would put most of every push on rank 0, so the rows
+// are dealt cyclically instead — every owner gets the same share of the hot rows.  The full table the
+// key was initialised with is cut down at the first such push.
 void Store::shard_rsp_table(RspKey& k) {
   KV_CHECK(k.use_bitmap(), "sharded row-sparse keys are limited to 2^28 rows");
   k.rows_per_rank = (k.num_rows + world_ - 1) / world_;
-  k.row_lo = std::min<int64_t>(k.num_rows, static_cast<int64_t>(rank_) * k.rows_per_rank);
-  k.row_hi = std::min<int64_t>(k.num_rows, k.row_lo + k.rows_per_rank);
+  k.row_lo = rank_;
+  k.stride = world_;
+  k.nlocal = k.num_rows > rank_ ? (k.num_rows - rank_ + world_ - 1) / world_ : 0;
   const size_t rowb = 4 * static_cast<size_t>(k.row_len);
   DevBuf shard;
   // at least 2 MiB: an allocation of its own, so that its IPC handle maps exactly this shard
   shard.reserve(std::max<size_t>(rowb * static_cast<size_t>(k.rows_per_rank), 2u << 20));
   CUDA_OK(cudaMemsetAsync(shard.p, 0, shard.bytes, stream_));
-  if (k.row_hi > k.row_lo)
-    CUDA_OK(cudaMemcpyAsync(shard.p, k.table.as<char>() + rowb * static_cast<size_t>(k.row_lo),
-                            rowb * static_cast<size_t>(k.row_hi - k.row_lo), cudaMemcpyDeviceToDevice, stream_));
+  if (k.nlocal > 0)   // every world-th row, starting at row `rank`
+    CUDA_OK(cudaMemcpy2DAsync(shard.p, rowb, k.table.as<char>() + rowb * static_cast<size_t>(rank_),
+                              rowb * static_cast<size_t>(world_), rowb, static_cast<size_t>(k.nlocal),
+                              cudaMemcpyDeviceToDevice, stream_));
   CUDA_OK(cudaStreamSynchronize(stream_));
   k.table.release();
   std::swap(k.table.p, shard.p);
@@ -345,7 +351,8 @@ void Store::init_rsp(int key, DLManagedTensor* dense_value) {
   KV_CHECK(k->num_rows < (int64_t(1) << 32), "row-sparse tables are limited to 2^32 rows");
   k->bits = bits_for(k->num_rows);
   k->row_lo = 0;
-  k->row_hi = k->rows_per_rank = k->num_rows;
+  k->stride = 1;
+  k->nlocal = k->rows_per_rank = k->num_rows;
   k->table.reserve(static_cast<size_t>(v.numel) * 4 + 16);
   CUDA_OK(cudaMemcpyAsync(k->table.p, v.data, static_cast<size_t>(v.numel) * 4, cudaMemcpyDefault, stream_));
   if (world_ > 1 && !in_process_) {
@@ -531,11 +538,11 @@ void Store::push_rsp(int key, int ncopies, DLManagedTensor* const* idx, DLManage
     if (!direct) {
       k.ensure_bitmap();
       const int g = static_cast<int>(std::max<int64_t>(1, std::min<int64_t>((maxlen + 255) / 256, sm_count(device_) * 4)));
-      rsp_mark_kernel<int64_t, true><<<g, 256, 0, stream_>>>(src, k.num_rows, k.row_lo, k.row_hi,
+      rsp_mark_kernel<int64_t, true><<<g, 256, 0, stream_>>>(src, k.num_rows, k.row_lo, k.stride,
                                                            k.bitmap.as<uint32_t>(), k.err());
       CUDA_OK(cudaGetLastError());
       ++launches_;
-      compact_bitmap(k, k.row_lo, k.row_hi, stream_, &launches_);
+      compact_bitmap(k, k.row_lo, k.stride, k.nlocal, stream_, &launches_);
     }
     const int grid = static_cast<int>(std::max<int64_t>(
         1, std::min<int64_t>(exchange ? bound : (direct ? maxlen : total), sm_count(device_) * 16)));
@@ -546,12 +553,12 @@ void Store::push_rsp(int key, int ncopies, DLManagedTensor* const* idx, DLManage
     if (up.std_update) {
       // merged rows first (sum in device order), then one pass over EVERY row of this rank's shard
       if (exchange) KV_CHECK(bound <= k.c_cap, "internal: staging too small for the standard update");
-      launch_reduce2<kRspStore>(vec, false, grid, stream_, src, k, k.row_lo, k.row_hi, ov, oi, on, up);
-      const int g2 = static_cast<int>(std::max<int64_t>(1, std::min<int64_t>(k.row_hi - k.row_lo, sm_count(device_) * 16)));
+      launch_reduce2<kRspStore>(vec, false, grid, stream_, src, k, k.row_lo, k.stride, ov, oi, on, up);
+      const int g2 = static_cast<int>(std::max<int64_t>(1, std::min<int64_t>(k.nlocal, sm_count(device_) * 16)));
 #define STD(MODE)                                                                                             \
   do {                                                                                                        \
-    if (vec) rsp_std_update_kernel<MODE, true><<<g2, 128, 0, stream_>>>(oi, on, ov, k.row_len, k.row_lo, k.row_hi, up);  \
-    else rsp_std_update_kernel<MODE, false><<<g2, 128, 0, stream_>>>(oi, on, ov, k.row_len, k.row_lo, k.row_hi, up);     \
+    if (vec) rsp_std_update_kernel<MODE, true><<<g2, 128, 0, stream_>>>(oi, on, ov, k.row_len, k.row_lo, k.stride, k.nlocal, up);  \
+    else rsp_std_update_kernel<MODE, false><<<g2, 128, 0, stream_>>>(oi, on, ov, k.row_len, k.row_lo, k.stride, k.nlocal, up);     \
   } while (0)
       if (up.mode == kRspSgd) STD(kRspSgd);
       else STD(kRspAdam);
@@ -565,10 +572,10 @@ void Store::push_rsp(int key, int ncopies, DLManagedTensor* const* idx, DLManage
       return;
     }
     switch (up.mode) {
-      case kRspStore: launch_reduce2<kRspStore>(vec, direct, grid, stream_, src, k, k.row_lo, k.row_hi, ov, oi, on, up); break;
-      case kRspSgd: launch_reduce2<kRspSgd>(vec, direct, grid, stream_, src, k, k.row_lo, k.row_hi, ov, oi, on, up); break;
-      case kRspAdam: launch_reduce2<kRspAdam>(vec, direct, grid, stream_, src, k, k.row_lo, k.row_hi, ov, oi, on, up); break;
-      default: launch_reduce2<kRspAdagrad>(vec, direct, grid, stream_, src, k, k.row_lo, k.row_hi, ov, oi, on, up); break;
+      case kRspStore: launch_reduce2<kRspStore>(vec, direct, grid, stream_, src, k, k.row_lo, k.stride, ov, oi, on, up); break;
+      case kRspSgd: launch_reduce2<kRspSgd>(vec, direct, grid, stream_, src, k, k.row_lo, k.stride, ov, oi, on, up); break;
+      case kRspAdam: launch_reduce2<kRspAdam>(vec, direct, grid, stream_, src, k, k.row_lo, k.stride, ov, oi, on, up); break;
+      default: launch_reduce2<kRspAdagrad>(vec, direct, grid, stream_, src, k, k.row_lo, k.stride, ov, oi, on, up); break;
     }
     ++launches_;
     if (exchange) {   // every owner has finished reading the senders' staging areas; all shards are updated
@@ -668,10 +675,10 @@ int64_t Store::row_sparse_pull(int key, DLManagedTensor* row_ids, DLManagedTenso
       KV_CHECK(k.peer_table[r] != nullptr, "internal: the shard of rank " << r << " is not mapped");
       tabs.t[r] = k.peer_table[r];
     }
-    tabs.rows_per_rank = k.rows_per_rank;
+    tabs.nranks = world_;
   } else {
     tabs.t[0] = k.table.as<float>();
-    tabs.rows_per_rank = k.num_rows;
+    tabs.nranks = 1;
   }
   if (k.use_bitmap()) {
     // mark -> chained popcount scan (emits the ids in ascending order) -> gather: 3 launches
@@ -684,12 +691,12 @@ int64_t Store::row_sparse_pull(int key, DLManagedTensor* row_ids, DLManagedTenso
     src.len[0] = total;
     const int g = std::min((nn + 255) / 256, sm_count(device_) * 4);
     uint32_t* bm = k.bitmap.as<uint32_t>();
-    if (ids.dtype == kI64) rsp_mark_kernel<int64_t, false><<<g, 256, 0, stream_>>>(src, k.num_rows, 0, k.num_rows, bm, k.err());
-    else if (ids.dtype == kI32) rsp_mark_kernel<int32_t, false><<<g, 256, 0, stream_>>>(src, k.num_rows, 0, k.num_rows, bm, k.err());
-    else rsp_mark_kernel<float, false><<<g, 256, 0, stream_>>>(src, k.num_rows, 0, k.num_rows, bm, k.err());
+    if (ids.dtype == kI64) rsp_mark_kernel<int64_t, false><<<g, 256, 0, stream_>>>(src, k.num_rows, 0, 1, bm, k.err());
+    else if (ids.dtype == kI32) rsp_mark_kernel<int32_t, false><<<g, 256, 0, stream_>>>(src, k.num_rows, 0, 1, bm, k.err());
+    else rsp_mark_kernel<float, false><<<g, 256, 0, stream_>>>(src, k.num_rows, 0, 1, bm, k.err());
     CUDA_OK(cudaGetLastError());
     ++launches_;
-    compact_bitmap(k, 0, k.num_rows, stream_, &launches_);
+    compact_bitmap(k, 0, 1, k.num_rows, stream_, &launches_);
     if (nnr_dev == nullptr) {
       if (k.host_count == nullptr) {
         CUDA_OK(cudaMallocHost(reinterpret_cast<void**>(&k.host_count), 16));

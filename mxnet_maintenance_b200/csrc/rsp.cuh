@@ -399,18 +399,20 @@ __device__ __forceinline__ int64_t rsp_len(const RspSources& in, int k) {
   return in.len_ptr[k] != nullptr ? __ldcv(in.len_ptr[k]) : in.len[k];
 }
 
-// ids -> bitmap bits for the rows in [row_lo, row_hi).  I: element type of the id arrays.
+// ids -> bitmap bits for the rows this rank owns: ids row_lo + j*stride, j in [0, nlocal) (one GPU: all
+// rows; several ranks: the rows with id % W == rank — a CYCLIC partition, so that skewed (Zipf) ids
+// spread evenly over the owners).  I: element type of the id arrays.
 template <typename I, bool CHECK_SORTED>
-__global__ void rsp_mark_kernel(const RspSources in, int64_t num_rows, int64_t row_lo, int64_t row_hi,
+__global__ void rsp_mark_kernel(const RspSources in, int64_t num_rows, int64_t row_lo, int64_t stride,
                                 uint32_t* __restrict__ bitmap, uint32_t* __restrict__ err) {
-  const int64_t stride = static_cast<int64_t>(gridDim.x) * blockDim.x;
+  const int64_t gstride = static_cast<int64_t>(gridDim.x) * blockDim.x;
   for (int k = 0; k < in.n; ++k) {
     const I* ids = static_cast<const I*>(in.idx[k]);
     const int64_t len = rsp_len(in, k);
     // the trip count is the same for every lane of a warp (i0 is the warp's lane-0 index), so the
     // full-mask warp primitives below are legal
     for (int64_t i0 = blockIdx.x * static_cast<int64_t>(blockDim.x) + (threadIdx.x & ~31); i0 < len;
-         i0 += stride) {
+         i0 += gstride) {
       const int64_t i = i0 + (threadIdx.x & 31);
       bool mine = i < len;
       int64_t b = 0;
@@ -422,8 +424,8 @@ __global__ void rsp_mark_kernel(const RspSources in, int64_t num_rows, int64_t r
         } else {
           if (CHECK_SORTED && i > 0 && static_cast<int64_t>(ids[i - 1]) >= id)
             atomicOr(err, static_cast<uint32_t>(kRspErrOrder));
-          mine = id >= row_lo && id < row_hi;
-          b = id - row_lo;
+          mine = id >= row_lo && (id - row_lo) % stride == 0;
+          b = (id - row_lo) / stride;
         }
       }
       // duplicate-heavy id lists (Zipf) would hammer a few words with atomics: lanes that hit the same
@@ -444,7 +446,8 @@ __global__ void rsp_mark_kernel(const RspSources in, int64_t num_rows, int64_t r
 // launch, so nothing is ever reset.
 // Emits the ids in ascending order, writes the total to count[0] and zeroes the bitmap.
 __global__ void __launch_bounds__(256)
-rsp_compact_kernel(uint32_t* __restrict__ bitmap, int nwords, int64_t row_lo, int64_t* __restrict__ uniq,
+rsp_compact_kernel(uint32_t* __restrict__ bitmap, int nwords, int64_t row_lo, int64_t stride,
+                   int64_t* __restrict__ uniq,
                    int64_t* __restrict__ count, volatile uint32_t* chain, uint32_t epoch) {
   __shared__ uint32_t ws[8];
   __shared__ uint32_t s_prefix;
@@ -502,10 +505,10 @@ rsp_compact_kernel(uint32_t* __restrict__ bitmap, int nwords, int64_t row_lo, in
 #pragma unroll
   for (int j = 0; j < 4; ++j) {
     uint32_t bits = w[j];
-    const int64_t base = row_lo + (static_cast<int64_t>(w0) + j) * 32;
+    const int64_t base = (static_cast<int64_t>(w0) + j) * 32;
     while (bits) {
       const int b = __ffs(bits) - 1;
-      uniq[pos++] = base + b;
+      uniq[pos++] = row_lo + (base + b) * stride;
       bits &= bits - 1;
     }
   }
@@ -514,12 +517,12 @@ rsp_compact_kernel(uint32_t* __restrict__ bitmap, int nwords, int64_t row_lo, in
 // One CTA per output row.  DIRECT: a single pushed copy — its index list is the merged set and source
 // row r is output row r.  Otherwise the row's id is looked up in every source by binary search
 // (thread k searches source k); rows are added in source order = the reference's device order
-// (ndarray_function.cc:81-113).  `up.table` / states start at row row_lo (this rank's shard).
+// (ndarray_function.cc:81-113).  `up.table` / states hold this rank's rows (id = row_lo + j*stride) densely.
 // MODE kRspStore: merged rows go to out_val[r], ids to out_idx[r], the row count to out_nnr.
 template <int MODE, bool VEC, bool DIRECT>
 __global__ void __launch_bounds__(128)
 rsp_reduce2_kernel(const RspSources in, const int64_t* __restrict__ uniq, const int64_t* __restrict__ count,
-                   int64_t row_len, int64_t num_rows, int64_t row_lo, int64_t row_hi, float* __restrict__ out_val,
+                   int64_t row_len, int64_t num_rows, int64_t row_lo, int64_t stride, float* __restrict__ out_val,
                    int64_t* __restrict__ out_idx, int64_t* __restrict__ out_nnr, const RspUpdate up,
                    uint32_t* __restrict__ err) {
   __shared__ int64_t s_pos[kMaxSources];
@@ -537,7 +540,7 @@ rsp_reduce2_kernel(const RspSources in, const int64_t* __restrict__ uniq, const 
         if (threadIdx.x == 0) atomicOr(err, static_cast<uint32_t>(kRspErrOrder));
         bad = true;
       }
-      if (bad || (MODE != kRspStore && (row < row_lo || row >= row_hi))) continue;
+      if (bad) continue;   // (the direct form is only used when this rank owns every row)
     } else {
       row = uniq[r];
       __syncthreads();   // the previous row's readers are done with s_pos
@@ -575,7 +578,7 @@ rsp_reduce2_kernel(const RspSources in, const int64_t* __restrict__ uniq, const 
 #pragma unroll
         for (int j = 0; j < W; ++j) out_val[r * row_len + c + j] = acc[j];
       } else {
-        const int64_t o = (row - row_lo) * row_len + c;
+        const int64_t o = ((row - row_lo) / stride) * row_len + c;
 #pragma unroll
         for (int j = 0; j < W; ++j) rsp_update_elem<MODE>(up, o + j, acc[j]);
       }
@@ -589,12 +592,13 @@ rsp_reduce2_kernel(const RspSources in, const int64_t* __restrict__ uniq, const 
 template <int MODE, bool VEC>
 __global__ void __launch_bounds__(128)
 rsp_std_update_kernel(const int64_t* __restrict__ midx, const int64_t* __restrict__ nnr_ptr,
-                      const float* __restrict__ mval, int64_t row_len, int64_t row_lo, int64_t row_hi,
+                      const float* __restrict__ mval, int64_t row_len, int64_t row_lo, int64_t stride, int64_t nlocal,
                       const RspUpdate up) {
   __shared__ int64_t s_pos;
   const int64_t nnr = nnr_ptr[0];
   constexpr int W = VEC ? 4 : 1;
-  for (int64_t row = row_lo + blockIdx.x; row < row_hi; row += gridDim.x) {
+  for (int64_t jrow = blockIdx.x; jrow < nlocal; jrow += gridDim.x) {
+    const int64_t row = row_lo + jrow * stride;
     __syncthreads();
     if (threadIdx.x == 0) {
       int64_t lo = 0, hi = nnr - 1, found = -1;
@@ -620,7 +624,7 @@ rsp_std_update_kernel(const int64_t* __restrict__ midx, const int64_t* __restric
           g[0] = mval[p * row_len + c];
         }
       }
-      const int64_t o = (row - row_lo) * row_len + c;
+      const int64_t o = jrow * row_len + c;
 #pragma unroll
       for (int j = 0; j < W; ++j) rsp_update_elem<MODE>(up, o + j, g[j]);
     }
@@ -630,11 +634,11 @@ rsp_std_update_kernel(const int64_t* __restrict__ midx, const int64_t* __restric
 // ---- row gather for row_sparse_pull ------------------------------------------------------------------
 // full != 0: the store holds every row (dense table); otherwise (src_idx, src_val) is a compact
 // row-sparse value and absent rows come back as zeros.
-// the table may be range-partitioned over the ranks: rows [o*rows_per_rank, (o+1)*rows_per_rank) live
-// in t[o] (peer memory for o != this rank); one GPU: t[0] holds everything
+// the table may be partitioned cyclically over W ranks: row id lives in t[id % W] (peer memory for the
+// other ranks) at local row id / W; one GPU: W = 1, t[0] holds everything
 struct RspTables {
   const float* t[kMaxCopies];
-  int64_t rows_per_rank;
+  int64_t nranks;
 };
 
 template <bool VEC>
@@ -650,8 +654,8 @@ rsp_gather_kernel(const int64_t* __restrict__ uniq, const int64_t* __restrict__ 
     const float* src = nullptr;
     if (full) {
       if (id >= 0 && id < num_rows) {
-        const int64_t o = id / tabs.rows_per_rank;
-        src = tabs.t[o] + (id - o * tabs.rows_per_rank) * row_len;
+        const int64_t o = id % tabs.nranks;
+        src = tabs.t[o] + (id / tabs.nranks) * row_len;
       }
     } else {
       int64_t lo = 0, hi = src_nnr[0] - 1;

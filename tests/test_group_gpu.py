@@ -238,7 +238,7 @@ def test_group_views_and_bound_step(oracle):
 def test_group_row_sparse(oracle, devs):
     """Row-sparse key in a group: one row-sparse gradient per device, union-sum in device order
     (ndarray_function.cc:81-113), lazy SGD-momentum rows, then row_sparse_pull.  With an optimizer the
-    table and its momentum are range-partitioned over the members (3000 rows over 3 members also
+    table and its momentum are dealt cyclically (row id % members) over the members (3000 rows over 3 members also
     covers a ragged last shard)."""
     m = _mb()
     num_rows, row_len = 3001, 64

@@ -271,42 +271,41 @@ struct RspUpdate {
   float* s1;
 };
 
-// the lazy row update of one element: table[o], s0[o], s1[o] <- gradient g
+// the row update of one element held in registers: (w, s0, s1) <- gradient g
 template <int MODE>
-__device__ __forceinline__ void rsp_update_elem(const RspUpdate& up, int64_t o, float g) {
-  float w = up.table[o];
+__device__ __forceinline__ void rsp_update_val(const RspUpdate& up, float& w, float& s0, float& s1, float g) {
   if (MODE == kRspSgd) {
     if (up.has_mom) {
       // SGDMomDnsRspDnsKernel (optimizer_op-inl.h:747-774): rate = lr*wd;
       // mom = momentum*mom - rate*w - lr*clip(rescale*g) | lr*rescale*g;  w += mom
-      float mom = up.s0[o];
+      float mom = s0;
       const float a = __fmul_rn(up.momentum, mom);
       const float bb = __fmul_rn(__fmul_rn(up.lr, up.wd), w);
       const float cc = up.clip >= 0.f ? __fmul_rn(up.lr, clipf(__fmul_rn(up.rescale, g), up.clip))
                                       : __fmul_rn(__fmul_rn(up.lr, up.rescale), g);
       mom = __fsub_rn(__fsub_rn(a, bb), cc);
-      up.s0[o] = mom;
-      up.table[o] = __fadd_rn(w, mom);
+      s0 = mom;
+      w = __fadd_rn(w, mom);
     } else {
       // SGDDnsRspKernel (optimizer_op-inl.h:452-475): (1 - lr*wd)*w - lr*clip(rescale*g) | (lr*rescale)*g
       // — NOT the multi-tensor op's mom = 0 form, which rounds differently
       const float keep = __fmul_rn(__fsub_rn(1.f, __fmul_rn(up.lr, up.wd)), w);
       const float step = up.clip >= 0.f ? __fmul_rn(up.lr, clipf(__fmul_rn(up.rescale, g), up.clip))
                                         : __fmul_rn(__fmul_rn(up.lr, up.rescale), g);
-      up.table[o] = __fsub_rn(keep, step);
+      w = __fsub_rn(keep, step);
     }
   } else if (MODE == kRspAdagrad) {
     // AdagradDnsRspDnsKernel (optimizer_op-inl.h:2514-2539): h += g'^2; w -= g'/sqrt(h+eps) * lr
     float gr = __fmul_rn(g, up.rescale);
     if (up.clip >= 0.f) gr = clipf(gr, up.clip);
-    const float h = __fadd_rn(up.s0[o], __fmul_rn(gr, gr));
-    up.s0[o] = h;
+    const float h = __fadd_rn(s0, __fmul_rn(gr, gr));
+    s0 = h;
     const float div = __fdiv_rn(gr, __fsqrt_rn(__fadd_rn(h, up.eps)));
-    up.table[o] = __fsub_rn(w, __fmul_rn(div, up.lr));
+    w = __fsub_rn(w, __fmul_rn(div, up.lr));
   } else if (MODE == kRspAdam) {
     // AdamDnsRspDnsKernel<cpu> (optimizer_op-inl.h:1352-1382): note (1-beta2)*square(clip(g)) with
     // clipping but (1-beta2)*g*g (left to right) without
-    float m = up.s0[o], v = up.s1[o];
+    float m = s0, v = s1;
     float gr = __fadd_rn(__fmul_rn(g, up.rescale), __fmul_rn(w, up.wd));
     const float omb1 = __fsub_rn(1.f, up.beta1), omb2 = __fsub_rn(1.f, up.beta2);
     if (up.clip >= 0.f) {
@@ -320,9 +319,49 @@ __device__ __forceinline__ void rsp_update_elem(const RspUpdate& up, int64_t o, 
       m = __fadd_rn(__fmul_rn(up.beta1, m), __fmul_rn(omb1, gr));
       v = __fadd_rn(__fmul_rn(up.beta2, v), __fmul_rn(__fmul_rn(omb2, gr), gr));
     }
-    up.s0[o] = m;
-    up.s1[o] = v;
-    up.table[o] = __fsub_rn(w, __fdiv_rn(__fmul_rn(up.lr, m), __fadd_rn(__fsqrt_rn(v), up.eps)));
+    s0 = m;
+    s1 = v;
+    w = __fsub_rn(w, __fdiv_rn(__fmul_rn(up.lr, m), __fadd_rn(__fsqrt_rn(v), up.eps)));
+  }
+}
+
+// W consecutive elements (W = 4: one 128-bit load / store per array) of a row at table offset o
+template <int MODE, int W>
+__device__ __forceinline__ void rsp_update_vec(const RspUpdate& up, int64_t o, const float (&g)[W]) {
+  constexpr bool kS0 = MODE == kRspSgd || MODE == kRspAdam || MODE == kRspAdagrad;
+  constexpr bool kS1 = MODE == kRspAdam;
+  const bool use_s0 = kS0 && (MODE != kRspSgd || up.has_mom);
+  float w[W], s0[W], s1[W];
+  if constexpr (W == 4) {
+    const float4 a = *reinterpret_cast<const float4*>(up.table + o);
+    w[0] = a.x; w[1] = a.y; w[2] = a.z; w[3] = a.w;
+    if (use_s0) { const float4 b = *reinterpret_cast<const float4*>(up.s0 + o); s0[0] = b.x; s0[1] = b.y; s0[2] = b.z; s0[3] = b.w; }
+    if (kS1) { const float4 c = *reinterpret_cast<const float4*>(up.s1 + o); s1[0] = c.x; s1[1] = c.y; s1[2] = c.z; s1[3] = c.w; }
+  } else {
+#pragma unroll
+    for (int j = 0; j < W; ++j) {
+      w[j] = up.table[o + j];
+      if (use_s0) s0[j] = up.s0[o + j];
+      if (kS1) s1[j] = up.s1[o + j];
+    }
+  }
+#pragma unroll
+  for (int j = 0; j < W; ++j) {
+    if (!use_s0) s0[j] = 0.f;
+    if (!kS1) s1[j] = 0.f;
+    rsp_update_val<MODE>(up, w[j], s0[j], s1[j], g[j]);
+  }
+  if constexpr (W == 4) {
+    *reinterpret_cast<float4*>(up.table + o) = make_float4(w[0], w[1], w[2], w[3]);
+    if (use_s0) *reinterpret_cast<float4*>(up.s0 + o) = make_float4(s0[0], s0[1], s0[2], s0[3]);
+    if (kS1) *reinterpret_cast<float4*>(up.s1 + o) = make_float4(s1[0], s1[1], s1[2], s1[3]);
+  } else {
+#pragma unroll
+    for (int j = 0; j < W; ++j) {
+      up.table[o + j] = w[j];
+      if (use_s0) up.s0[o + j] = s0[j];
+      if (kS1) up.s1[o + j] = s1[j];
+    }
   }
 }
 
@@ -364,8 +403,7 @@ rsp_reduce_kernel(const RspInputs in, const uint32_t* __restrict__ pay, const in
         for (int j = 0; j < W; ++j) out_val[r * row_len + c + j] = acc[j];
       } else {
         const int64_t o = row * row_len + c;
-#pragma unroll
-        for (int j = 0; j < W; ++j) rsp_update_elem<MODE>(up, o + j, acc[j]);
+        rsp_update_vec<MODE, W>(up, o, acc);
       }
     }
   }
@@ -579,8 +617,7 @@ rsp_reduce2_kernel(const RspSources in, const int64_t* __restrict__ uniq, const 
         for (int j = 0; j < W; ++j) out_val[r * row_len + c + j] = acc[j];
       } else {
         const int64_t o = ((row - row_lo) / stride) * row_len + c;
-#pragma unroll
-        for (int j = 0; j < W; ++j) rsp_update_elem<MODE>(up, o + j, acc[j]);
+        rsp_update_vec<MODE, W>(up, o, acc);
       }
     }
   }
@@ -625,8 +662,7 @@ rsp_std_update_kernel(const int64_t* __restrict__ midx, const int64_t* __restric
         }
       }
       const int64_t o = jrow * row_len + c;
-#pragma unroll
-      for (int j = 0; j < W; ++j) rsp_update_elem<MODE>(up, o + j, g[j]);
+      rsp_update_vec<MODE, W>(up, o, g);
     }
   }
 }

@@ -98,8 +98,19 @@ __device__ __forceinline__ float mc_ld1(const float* p) {
 __device__ __forceinline__ void mc_st1(float* p, float v) {
   asm volatile("multimem.st.relaxed.sys.global.f32 [%0], %1;" ::"l"(p), "f"(v) : "memory");
 }
-// fp16 buckets never take the multicast path (the switch's half additions round differently from the
-// reference's): fp16 kernels are compiled without any multimem code.
+// fp16 buckets: the switch adds the W half values in fp32 and rounds ONCE (.acc::f32), where the
+// reference rounds to half after every add — within the fp16 tolerance (rtol 2e-3), not bit for bit.
+// Only vector forms exist (the store pads multicast chunks to whole 4-element vectors).
+__device__ __forceinline__ void mc_ld_raw(const __half* p, Raw<__half>& r) {
+  asm volatile("multimem.ld_reduce.relaxed.sys.global.add.acc::f32.v2.f16x2 {%0,%1}, [%2];"
+               : "=r"(r.v.x), "=r"(r.v.y) : "l"(p) : "memory");
+}
+__device__ __forceinline__ void mc_st4(__half* p, const float (&v)[4]) {
+  const __half2 a = __floats2half2_rn(v[0], v[1]);
+  const __half2 b = __floats2half2_rn(v[2], v[3]);
+  asm volatile("multimem.st.relaxed.sys.global.v2.f16x2 [%0], {%1,%2};" ::"l"(p),
+               "r"(*reinterpret_cast<const uint32_t*>(&a)), "r"(*reinterpret_cast<const uint32_t*>(&b)) : "memory");
+}
 
 // value of x after a round trip through the tensor's element type
 template <typename T> __device__ __forceinline__ float round_to(float x);
@@ -139,13 +150,15 @@ template <typename T, int NG>
 __device__ __forceinline__ void grad_load(const MtaArgs& a, const T* const* gp, int64_t e,
                                           Raw<T> (&r)[NG > 0 ? NG : 1]) {
   if constexpr (NG == 1) {
-    if constexpr (sizeof(T) == 4) {   // NVLS is fp32 only: fp16 kernels carry no multimem code at all
-      if (a.sync_mode & kSyncMcGrad) {
+    if (a.sync_mode & kSyncMcGrad) {   // NVLS: the switch returns the sum over all ranks
+      if constexpr (sizeof(T) == 4) {
         float v[4];
         mc_ld4(gp[0] + e, v);
         r[0].v = make_float4(v[0], v[1], v[2], v[3]);
-        return;
+      } else {
+        mc_ld_raw(gp[0] + e, r[0]);
       }
+      return;
     }
     ldraw(gp[0] + e, r[0]);
   } else if constexpr (NG > 1) {
@@ -197,6 +210,8 @@ template <typename T, int NG>
 __device__ __forceinline__ float grad1(const MtaArgs& a, int t, int64_t e) {
   if constexpr (NG == 1 && sizeof(T) == 4) {
     if (a.sync_mode & kSyncMcGrad) return mc_ld1(reinterpret_cast<const T*>(sec_grad(a, 0)[t]) + e);
+  } else if constexpr (NG == 1) {
+    if (a.sync_mode & kSyncMcGrad) __trap();   // no scalar fp16 multimem form; multicast chunks are whole vectors
   }
   float g = ld1(reinterpret_cast<const T*>(sec_grad(a, 0)[t]) + e);
   if (NG != 1) {
@@ -679,11 +694,8 @@ mta_kernel(const MtaArgs a, const Op op, const float* __restrict__ gscale,
           if (F.write_s1) st4(s1p + e, s1[u]);
           if (F.write_w) st4(wp + e, w[u]);
           if (F.write_out) {
-            bool mc = false;
-            if constexpr (sizeof(T) == 4) {
-              mc = (a.sync_mode & kSyncMcOut) != 0;
-              if (mc) mc_st4(reinterpret_cast<T*>(sec_out(a, 0)[t]) + e, w[u]);
-            }
+            const bool mc = (a.sync_mode & kSyncMcOut) != 0;
+            if (mc) mc_st4(reinterpret_cast<T*>(sec_out(a, 0)[t]) + e, w[u]);
             if (!mc)
               for (int k = 0; k < a.nout; ++k) st4(reinterpret_cast<T*>(sec_out(a, k)[t]) + e, w[u]);
           }
@@ -711,6 +723,8 @@ mta_kernel(const MtaArgs a, const Op op, const float* __restrict__ gscale,
         if constexpr (sizeof(T) == 4) {
           mc = (a.sync_mode & kSyncMcOut) != 0;
           if (mc) mc_st1(reinterpret_cast<T*>(sec_out(a, 0)[t]) + e, w);
+        } else if (a.sync_mode & kSyncMcOut) {
+          __trap();
         }
         if (!mc)
           for (int k = 0; k < a.nout; ++k) st1(reinterpret_cast<T*>(sec_out(a, k)[t]) + e, w);

@@ -815,11 +815,11 @@ void Store::run_class_p2p(DensePlan& p, Segment& s, const std::vector<const Entr
   // 0.254 ms vs 0.325 ms per step at 8 GPUs, but 0.303 vs 0.193 ms at 2 GPUs (where it saves no
   // link bytes), and slower for LAMB (whose shard is first reduced into the local bucket anyway).
   // Default: on from 4 ranks for single-pass optimizers; B200KV_NVLS=1 / 0 forces it on / off.
-  // fp32 only: the switch's fp16 additions round differently from the reference's half adds.
   static const int nvls_env = [] { const char* e = getenv("B200KV_NVLS"); return e ? (e[0] == '1' ? 1 : 0) : -1; }();
   const bool nvls_want = nvls_env == 1 || (nvls_env == -1 && W >= 4 && !prereduce);
-  const bool nvls = nvls_want && P.symmetric && P.mc_g != nullptr && P.mc_w != nullptr && !staged && !push_rs &&
-                    s.dtype == kF32;
+  // fp16 buckets too: the switch accumulates in fp32 and rounds once — within the fp16 tolerance of the
+  // reference's half adds, not bit for bit (B200KV_NVLS=0 keeps the bit-exact peer path)
+  const bool nvls = nvls_want && P.symmetric && P.mc_g != nullptr && P.mc_w != nullptr && !staged && !push_rs;
   // gradient copy k of the element at flat offset `off`, as seen by the shard owner
   auto grad_src = [&](int k, int64_t off) -> const char* {
     if (!push_rs) return static_cast<const char*>(P.g[k]) + off * es;

@@ -232,8 +232,11 @@ def main():
     for k in keys:
         for which, want in model3.states_of(k).items():
             have = kv3.get_state(k, which)
-            if have is None or not np.array_equal(have.reshape(-1), want):
-                failures.append("mp-adam state %d of key %d" % (which, k))
+            exact3 = kv3.last_exchange() in ("peer", "peer-push") or world == 2
+            good = have is not None and (np.array_equal(have.reshape(-1), want) if exact3 else
+                                         np.allclose(have.reshape(-1), want, rtol=2e-3, atol=1e-5))
+            if not good:
+                failures.append("mp-adam state %d of key %d (%s)" % (which, k, kv3.last_exchange()))
 
     # ---- the BASELINE configurations at full size: bench.py's own pre-flight (weights of every rank
     # and all gathered optimizer states vs the CommCPU + reference-functor oracle)

@@ -494,6 +494,20 @@ def run_rsp(args, env, steps, e2e_steps, cpu_baseline):
         env.clocks.active = False
     ms = env.max_over_ranks(e0.elapsed_time(e1))
     launches = kv.launch_count() - l0
+    # the same step with the engine-style pull (row count left on the device, no host wait inside)
+    out_a = mb.RowSparse(None, None, (0, 0))
+    for i in range(3):
+        kv.push(0, [sets[i % nvar][0]])
+        kv.row_sparse_pull(0, out=out_a, row_ids=sets[i % nvar][1], sync=False)
+    env.barrier()
+    a0, a1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    a0.record()
+    for i in range(steps):
+        kv.push(0, [sets[i % nvar][0]])
+        kv.row_sparse_pull(0, out=out_a, row_ids=sets[i % nvar][1], sync=False)
+    a1.record()
+    env.barrier()
+    ms_async = env.max_over_ranks(a0.elapsed_time(a1)) / steps
     # e2e: host ids + rows in, pulled rows out
     h = [(s[0].data.cpu().pin_memory(), s[0].indices.cpu().pin_memory(), s[1].cpu().pin_memory()) for s in sets]
 
@@ -532,7 +546,9 @@ def run_rsp(args, env, steps, e2e_steps, cpu_baseline):
                                "(sort + unique + gather): whole step",
                      "algorithmic_bytes_per_step": alg, "peak_source": peak_src,
                      "launches_per_step": launches / steps,
-                     "note": "whole-step time incl. the row-count read-back that row_sparse_pull needs"},
+                     "note": "whole-step time incl. the row-count read-back that row_sparse_pull needs",
+                     "ms_per_step_async_pull": ms_async,
+                     "frac_async_pull": alg / (ms_async * 1e-3) / 1e9 / peak},
         "e2e": {"value": e2e_steps / e2e_s, "unit": "steps/s",
                 "h2d_bytes_per_step": int(nnr / world * (8 + 4 * row_len) + 8 * nids),
                 "d2h_bytes_per_step": int(uniq_pull * 4 * row_len), "steps": e2e_steps},

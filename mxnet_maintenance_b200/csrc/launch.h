@@ -21,6 +21,9 @@ struct MtaCall {
   // path on one device): every kernel that may wait on a peer takes 1/grid_div of the persistent
   // grid so that all ranks' kernels are resident together
   int grid_div = 1;
+  // cap on resident CTAs per SM for this launch (0 = what the occupancy API allows): the NVSwitch
+  // multicast exchange runs faster with fewer requests in flight (tools/nvls_probe.cu)
+  int max_per_sm = 0;
 };
 
 struct OptScalars {

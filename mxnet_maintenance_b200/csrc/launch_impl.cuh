@@ -21,7 +21,7 @@ int grid_for(const MtaCall& c, K kernel) {
     if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, kernel, kThreads, 0) != cudaSuccess || n < 1) n = 2;
     per_sm = n;
   }
-  int g = sm_count(c.device) * per_sm;
+  int g = sm_count(c.device) * (c.max_per_sm > 0 ? std::min(per_sm, c.max_per_sm) : per_sm);
   if (c.grid_div > 1) g = std::max(1, g / c.grid_div);
   return c.plan->nchunks < g ? (c.plan->nchunks > 0 ? c.plan->nchunks : 1) : g;
 }

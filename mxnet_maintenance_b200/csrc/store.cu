@@ -933,6 +933,13 @@ void Store::run_class_p2p(DensePlan& p, Segment& s, const std::vector<const Entr
   u.blob = dev + o_upd; u.ngrad = upd_ng; u.nout = upd_no; u.plan = &p.shard; u.staged = staged && !prereduce;
   if (fold) { u.sync = dsync; u.epoch = f.epoch; u.sync_mode = (prereduce ? 0 : kSyncWaitReady) | kSyncSignalDone; }
   if (nvls) u.sync_mode |= kSyncMcOut | (prereduce ? 0 : kSyncMcGrad);
+  // CTAs per SM of the exchange kernel (0 = what fits).  A bare switch-reduce + multicast loop is fastest
+  // with ONE CTA per SM (tools/nvls_probe.cu, profiles/r2_nvls_probe.txt: 0.216 ms against 0.256 ms with
+  // four at 8 GPUs), but the update kernel measured the same with 1, 2 or all resident CTAs
+  // (profiles/r2_sweep_ctas_n4.txt), so the default stays "what fits"; the knobs remain for tuning.
+  static const int nvls_ctas = [] { const char* e = getenv("B200KV_NVLS_CTAS"); return e ? atoi(e) : 0; }();
+  static const int peer_ctas = [] { const char* e = getenv("B200KV_PEER_CTAS"); return e ? atoi(e) : 0; }();
+  u.max_per_sm = nvls ? nvls_ctas : peer_ctas;
   prof_begin(0);
   if (has_opt()) {
     const float* gscale = opt_.clip_global_norm >= 0.f ? global_norm_scale(p, p.shard, u) : nullptr;

@@ -4,6 +4,7 @@
 #include "group.h"
 
 #include <algorithm>
+#include <cstdlib>
 #include <cstring>
 
 namespace b200kv {
@@ -45,10 +46,21 @@ Group::Group(int ndev, const int* dev_ids) {
       DeviceGuard g(dev_ids[i]);
       preload_kernels();   // no lazy kernel load may fall between two members' launches (common.h)
     }
+  {
+    // same rule as Store::run_class_p2p: the switch exchange pays from 4 GPUs, B200KV_NVLS=1 / 0 forces it on / off
+    const char* e = getenv("B200KV_NVLS");
+    const bool want = e ? e[0] == '1' : ndev >= 4;
+    if (ndev > 1 && want) arena_ = McArena::create(std::vector<int>(dev_ids, dev_ids + ndev));
+    mc_ctx_.resize(ndev);
+  }
   for (int i = 0; i < ndev; ++i) {
     const int share = static_cast<int>(std::count(dev_ids, dev_ids + ndev, dev_ids[i]));
     m_.emplace_back(new Store(dev_ids[i], i, ndev, /*in_process=*/ndev > 1, share));
     raw_.push_back(m_.back().get());
+    if (arena_) {
+      mc_ctx_[i] = McCtx{arena_.get(), i};
+      m_.back()->set_symmetric_allocator(&Group::mc_alloc, &mc_ctx_[i]);
+    }
     DeviceGuard g(dev_ids[i]);
     cudaStream_t s = nullptr;
     cudaEvent_t a = nullptr, b = nullptr;
@@ -65,6 +77,11 @@ Group::Group(int ndev, const int* dev_ids) {
     ev_in_.push_back(a);
     ev_out_.push_back(b);
   }
+}
+
+int Group::mc_alloc(void* ctx, size_t bytes, void** local, void** peers, void** mc) {
+  McCtx* c = static_cast<McCtx*>(ctx);
+  return c->arena->request(c->member, bytes, local, peers, mc) ? 0 : 1;
 }
 
 Group::~Group() {

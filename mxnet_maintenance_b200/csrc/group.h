@@ -4,7 +4,8 @@
 // param.list_grad() / list_data(), python/mxnet/gluon/trainer.py:392-395).
 //
 // A Group owns one Store per device ("member", rank i of W) and drives all of them from the caller's
-// thread.  Members exchange through peer memory only (cudaDeviceEnablePeerAccess; no IPC, no NCCL):
+// thread.  Members exchange through peer memory (cudaDeviceEnablePeerAccess; no IPC, no NCCL; from 4
+// distinct devices the buffers come from one NVSwitch multicast arena, mcast.h):
 // the SAME fused reduce-scatter + update + all-gather kernel as in the one-process-per-GPU mode is
 // launched once per member on that member's own stream, and its in-kernel flag barriers order the
 // members on the GPUs, never on the host.
@@ -13,6 +14,7 @@
 #include <unordered_map>
 #include <vector>
 
+#include "mcast.h"
 #include "store.h"
 
 namespace b200kv {
@@ -70,6 +72,15 @@ class Group : public KVHandle {
   void sync_members();
   void link_all();
 
+  // NVSwitch multicast memory for the members' weight segments and gradient buckets (from 4 distinct
+  // devices, or B200KV_NVLS=1); declared before the members so that it outlives them
+  struct McCtx {
+    McArena* arena;
+    int member;
+  };
+  static int mc_alloc(void* ctx, size_t bytes, void** local, void** peers, void** mc);
+  std::unique_ptr<McArena> arena_;
+  std::vector<McCtx> mc_ctx_;
   std::vector<std::unique_ptr<Store>> m_;
   std::vector<Store*> raw_;
   std::vector<cudaStream_t> own_, caller_;

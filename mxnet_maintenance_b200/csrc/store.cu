@@ -1271,6 +1271,15 @@ void Store::link_peers(int seg, const std::vector<Store*>& all) {
   Segment::P2P& P = s.p2p;
   if (P.ok) return;
   P.tried = true;
+  // the switch exchange only when EVERY member's bucket and weight segment sit behind the same multicast
+  // objects (Group's McArena); one member on plain memory puts all of them on the peer load/store path
+  bool all_mc = true;
+  for (int k = 0; k < world_; ++k) {
+    const Segment::P2P& o = all[k]->segs_[seg]->p2p;
+    all_mc = all_mc && o.mc_g != nullptr && o.mc_w != nullptr && o.mc_g == all[0]->segs_[seg]->p2p.mc_g &&
+             o.mc_w == all[0]->segs_[seg]->p2p.mc_w;
+  }
+  P.symmetric = all_mc;
   for (int k = 0; k < world_; ++k) {
     Segment& o = *all[k]->segs_[seg];
     KV_CHECK(o.total == s.total && o.dtype == s.dtype, "internal: members disagree on the segment layout");

@@ -146,10 +146,14 @@ __device__ __forceinline__ const uint64_t* sec(const MtaArgs& a, int s) {
 template <int NG> struct Unroll { static constexpr int value = NG <= 2 ? 4 : (NG <= 4 ? 2 : 1); };
 
 // phase 1: issue the loads of every gradient copy of one vector (nothing is converted or added yet)
-template <typename T, int NG>
+// MC = false compiles the multicast branch out (an instantiation that never runs over the switch keeps
+// its loads free of the `asm volatile` ordering point: fp16 Adam lost 3 % of its bandwidth to it)
+template <typename T, int NG, bool MC = true>
 __device__ __forceinline__ void grad_load(const MtaArgs& a, const T* const* gp, int64_t e,
                                           Raw<T> (&r)[NG > 0 ? NG : 1]) {
-  if constexpr (NG == 1) {
+  if constexpr (NG == 1 && !MC) {
+    ldraw(gp[0] + e, r[0]);
+  } else if constexpr (NG == 1) {
     if (a.sync_mode & kSyncMcGrad) {   // NVLS: the switch returns the sum over all ranks
       if constexpr (sizeof(T) == 4) {
         float v[4];
@@ -566,6 +570,13 @@ struct HasPrepT { static constexpr bool value = false; };
 template <class Op>
 struct HasPrepT<Op, decltype((void)&Op::prep_t)> { static constexpr bool value = true; };
 
+// fp16 buckets over the NVSwitch (one fp32-accumulated sum, rounded once) stay inside the fp16 tolerance
+// only where the step is linear in the gradient; Adam / AdaGrad normalise by it and never take that
+// exchange (Store::run_class_p2p), so their fp16 instantiations carry no multicast code
+template <class Op> struct Mc16 { static constexpr bool value = true; };
+template <> struct Mc16<AdamOp> { static constexpr bool value = false; };
+template <> struct Mc16<AdagradOp> { static constexpr bool value = false; };
+
 template <class Op>
 __device__ __forceinline__ typename Op::PT op_prep(const Op& op, float lr, float wd, float a0,
                                                    float a1, int t) {
@@ -608,6 +619,7 @@ __global__ void __launch_bounds__(kThreads, 2)
 mta_kernel(const MtaArgs a, const Op op, const float* __restrict__ gscale,
            float* __restrict__ partials) {
   constexpr OpFlags F = Op::F;
+  constexpr bool kMc = sizeof(T) == 4 || Mc16<Op>::value;   // may this instantiation run over the NVSwitch?
   __shared__ float sred[2][kThreads / 32];
   const int tid = threadIdx.x;
   const float gs = (F.read_g && gscale != nullptr) ? *gscale : 1.0f;
@@ -669,7 +681,7 @@ mta_kernel(const MtaArgs a, const Op op, const float* __restrict__ gscale,
         if (v < nvec) {
           const int64_t e = base + 4 * v;
           if (F.read_x) ld4(xp + e, x[u]);
-          if (F.read_g) grad_load<T, NG>(a, gp, e, gr[u]);
+          if (F.read_g) grad_load<T, NG, kMc>(a, gp, e, gr[u]);
           if (F.read_w) ldraw(wp + e, wr[u]);
           if (F.read_s0) ld4(s0p + e, s0[u]);
           if (F.read_s1) ld4(s1p + e, s1[u]);
@@ -694,8 +706,11 @@ mta_kernel(const MtaArgs a, const Op op, const float* __restrict__ gscale,
           if (F.write_s1) st4(s1p + e, s1[u]);
           if (F.write_w) st4(wp + e, w[u]);
           if (F.write_out) {
-            const bool mc = (a.sync_mode & kSyncMcOut) != 0;
-            if (mc) mc_st4(reinterpret_cast<T*>(sec_out(a, 0)[t]) + e, w[u]);
+            bool mc = false;
+            if constexpr (kMc) {
+              mc = (a.sync_mode & kSyncMcOut) != 0;
+              if (mc) mc_st4(reinterpret_cast<T*>(sec_out(a, 0)[t]) + e, w[u]);
+            }
             if (!mc)
               for (int k = 0; k < a.nout; ++k) st4(reinterpret_cast<T*>(sec_out(a, k)[t]) + e, w[u]);
           }

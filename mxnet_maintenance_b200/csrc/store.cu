@@ -820,9 +820,10 @@ void Store::run_class_p2p(DensePlan& p, Segment& s, const std::vector<const Entr
   // fp16 buckets: the switch accumulates in fp32 and rounds once, the reference rounds to half after
   // every add.  For SGD (the step is linear in the gradient) that stays inside the fp16 tolerance;
   // Adam / AdaGrad divide by |g|-like terms, so where the copies cancel the one-rounding sum moves the
-  // step by up to lr (measured: 28x the tolerance on BERT-base) — those stay on the bit-exact peer path
-  // unless B200KV_NVLS=1 asks for it.
-  const bool f16_ok = s.dtype == kF32 || !has_opt() || opt_.kind == B200KV_OPT_SGD || nvls_env == 1;
+  // step by up to lr (measured: 28x the tolerance on BERT-base) — those always stay on the bit-exact peer
+  // path (their fp16 kernels carry no multicast code, optim.cuh Mc16).
+  const bool f16_ok = s.dtype == kF32 || !has_opt() || opt_.kind == B200KV_OPT_SGD ||
+                      (nvls_env == 1 && opt_.kind == B200KV_OPT_LAMB);
   const bool nvls = nvls_want && f16_ok && P.symmetric && P.mc_g != nullptr && P.mc_w != nullptr && !staged && !push_rs;
   // gradient copy k of the element at flat offset `off`, as seen by the shard owner
   auto grad_src = [&](int k, int64_t off) -> const char* {
